@@ -1,0 +1,154 @@
+/*
+ * qlinear_b200.h -- C ABI of the B200-native (sm_100a) quantized-linear engine.
+ *
+ * This is the drop-in boundary for ONE hot path of songxxzp/nano-vllm-hw3: the INT8 / FP8
+ * (e4m3) per-row and per-group quantized linear layers.  Every entry point names the
+ * reference interface it replaces (paths relative to the reference repository root).  The
+ * reference is pure Python, so the binding a maintainer adds is a ctypes stub; it is shown
+ * in INTEGRATION.md and shipped as nano-vllm-hw3_b200/nanovllm/_ext.py.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers unless stated;
+ *   - every call is stream-ordered on `stream` (a cudaStream_t passed as void*), never
+ *     synchronises, never allocates device memory, keeps no per-call global state and is
+ *     safe inside CUDA-graph capture (the reference captures its decode step,
+ *     nanovllm/engine/model_runner.py:316-356);
+ *   - returns QL_OK (0) or a QL_ERR_* code; never throws, never aborts;
+ *   - there is NO CPU fallback: on a device that is not compute capability 10.0 every
+ *     compute entry point returns QL_ERR_UNSUPPORTED_ARCH.
+ *
+ * Layouts (identical to the reference's in-memory tensors)
+ *   x    bf16  [M, K], row stride ldx elements, K contiguous (16-byte aligned rows)
+ *   qx   1 B   [M, K] dense             int8 or e4m3 bit patterns
+ *   sx   fp32  [M]                      per-token scales
+ *   qw   1 B   [N, K] dense, K contiguous
+ *   sw   fp32  [N] (per-row, group == 0) or [N, K/group] row-major (per-group)
+ *   bias bf16  [N] or NULL
+ *   y    bf16  [M, N], row stride ldy elements
+ */
+#ifndef QLINEAR_B200_H_
+#define QLINEAR_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QL_ABI_VERSION 2
+
+/* status codes */
+#define QL_OK 0
+#define QL_ERR_BAD_FORMAT 1       /* fmt is not QL_INT8 / QL_FP8_E4M3 (reference: assert dtype in [...], quantization.py:151,203,353) */
+#define QL_ERR_BAD_SHAPE 2        /* K % 128 != 0 (quantization.py:328), K % group != 0 (:205), M > 16 for the GEMV, negative sizes */
+#define QL_ERR_MISALIGNED 3       /* pointer / stride alignment the kernels need (16 B) */
+#define QL_ERR_UNSUPPORTED_ARCH 4 /* current device is not sm_100 */
+#define QL_ERR_WORKSPACE 5        /* caller-provided workspace too small or NULL */
+#define QL_ERR_CUDA 6             /* a CUDA runtime/driver call failed (launch error, TMA descriptor encode) */
+#define QL_ERR_NULL 7             /* required pointer is NULL */
+
+/* element formats of the quantized tensors */
+#define QL_INT8 0     /* torch.int8,          qmax 127 */
+#define QL_FP8_E4M3 1 /* torch.float8_e4m3fn, qmax 448 */
+
+typedef void* ql_stream_t; /* cudaStream_t */
+
+#if defined(__GNUC__)
+#define QL_API __attribute__((visibility("default")))
+#else
+#define QL_API
+#endif
+
+/* ABI version of the loaded library (== QL_ABI_VERSION it was built with). */
+QL_API int ql_version(void);
+
+/* Static, NUL-terminated description of a status code. */
+QL_API const char* ql_status_string(int status);
+
+/* QL_OK when the current CUDA device can run the kernels (compute capability 10.x). */
+QL_API int ql_device_check(void);
+
+/*
+ * Per-row (per-token) symmetric quantiser.
+ * Replaces per_row_quant / _per_row_quant_kernel, nanovllm/utils/quantization.py:13-51,147-163:
+ *   amax = max(max_k |x[m,k]|, 1e-8); s[m] = amax/qmax; q = round_half_away(x * (qmax/amax))
+ *   (int8) or e4m3_rn(x * (qmax/amax)) (fp8).  Used for activations every forward and for
+ * weights once at load (QLinear.__init__, :355).
+ */
+QL_API int ql_quant_rows(const void* x, int64_t M, int64_t K, int64_t ldx, int fmt,
+                  void* q, float* s, ql_stream_t stream);
+
+/*
+ * Per-group weight quantiser (load time).
+ * Replaces per_group_quant, quantization.py:194-234 (torch semantics: s = amax/qmax,
+ * q = clamp(round_half_even(w / s), -128, 127) or e4m3(w / s)).  w is bf16 [N, K] dense,
+ * s is [N, K/group].  group == K gives the per-row layout of the reference's CPU path.
+ */
+QL_API int ql_quant_groups(const void* w, int64_t N, int64_t K, int64_t group, int fmt,
+                    void* q, float* s, ql_stream_t stream);
+
+/*
+ * Per-tensor quantiser (load time).
+ * Replaces per_tensor_quant, quantization.py:166-191: one scale for the whole tensor, kept in
+ * the input dtype (a bf16 scalar) and applied with a bf16 division, as torch does there:
+ *   scale = bf16(max(amax, 1e-8) / qmax); q = clamp(round_half_even(bf16(x / scale))) or e4m3(.)
+ * x is bf16, `numel` contiguous elements; scale_bf16 points at ONE bf16 value; workspace needs
+ * >= 4 bytes (the running amax).  Two stream-ordered kernels + one 4-byte memset.
+ */
+QL_API int ql_quant_tensor(const void* x, int64_t numel, int fmt, void* q, void* scale_bf16,
+                    void* workspace, size_t workspace_bytes, ql_stream_t stream);
+
+/*
+ * W8A8 GEMM on tcgen05 tensor cores with the scale/bias epilogue fused.
+ * group == 0: replaces _per_row_post_process_mm, quantization.py:54-144 (launched :330-345):
+ *   y[m,n] = bf16( float(sum_k qx[m,k]*qw[n,k]) * sx[m] * sw[n] + bias[n] )
+ * group > 0 (multiple of 128): the per-group W8A8 form that replaces per_group_matmul,
+ * quantization.py:265-307, on the GPU:
+ *   y[m,n] = bf16( sx[m] * sum_j sw[n,j] * float(sum_{k in block j} qx*qw) + bias[n] )
+ * Requires K % 128 == 0 (as the reference, :328).
+ */
+QL_API int ql_gemm_w8a8(const void* qx, const float* sx, const void* qw, const float* sw,
+                 const void* bias, void* y, int64_t ldy, int64_t M, int64_t N, int64_t K,
+                 int fmt, int64_t group, ql_stream_t stream);
+
+/*
+ * Parity entry point: raw int32 accumulators acc[m,n] = sum_k qx[m,k]*qw[n,k] of the same
+ * tcgen05 INT8 kernel (dense [M,N] int32).  Mirrors the `acc` tile of the reference kernel,
+ * quantization.py:96-106, which a bf16 output cannot prove equal.
+ */
+QL_API int ql_gemm_i8_acc(const void* qx, const void* qw, int32_t* acc, int64_t M, int64_t N,
+                   int64_t K, ql_stream_t stream);
+
+/*
+ * Decode-regime fused quantise + GEMV (M <= 16), one launch per linear.
+ * Replaces the per_row_quant + _per_row_post_process_mm pair of per_row_matmul,
+ * quantization.py:310-346, for small M (and the per-group form, as ql_gemm_w8a8).
+ * group == 0 or a multiple of 32 that divides K.  Same arithmetic as ql_quant_rows followed
+ * by ql_gemm_w8a8 (bit-identical for INT8 per-row).
+ */
+QL_API int ql_gemv_w8a8(const void* x, int64_t ldx, const void* qw, const float* sw, const void* bias,
+                 void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int fmt, int64_t group,
+                 ql_stream_t stream);
+
+/*
+ * One quantized linear, dispatched by M: the whole of per_row_matmul (quantization.py:310-346)
+ * / the W8A8 replacement of per_group_matmul (:265-307) behind QLinear.forward (:363-364) and
+ * QGroupLinear.forward (:400-401).  M <= 16 -> ql_gemv_w8a8; otherwise ql_quant_rows into
+ * `workspace` followed by ql_gemm_w8a8.  workspace must hold ql_workspace_bytes(M, K) bytes
+ * (may be NULL when that is 0).
+ */
+QL_API int ql_linear(const void* x, int64_t ldx, const void* qw, const float* sw, const void* bias,
+              void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int fmt, int64_t group,
+              void* workspace, size_t workspace_bytes, ql_stream_t stream);
+
+/* Bytes of caller-provided scratch ql_linear needs for an [M, K] activation (0 for M <= 16). */
+QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);
+
+/* Name of the kernel family ql_linear would pick ("gemv_mma", "gemm_tcgen05"); for logs/tests. */
+QL_API const char* ql_linear_path(int64_t M, int64_t N, int64_t K, int64_t group);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QLINEAR_B200_H_ */

@@ -1,0 +1,179 @@
+// C ABI of libqlinear_b200.so (see include/qlinear_b200.h): argument validation, device
+// check, dispatch by M.  No CPU fallback: anything but a compute-capability-10.x device gets
+// QL_ERR_UNSUPPORTED_ARCH.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ql {
+
+struct DevInfo {
+  int ok;   // 1 = sm_100-class device, 0 = something else, -1 = query failed
+  int sms;
+};
+
+static DevInfo query_device() {
+  // cached per device ordinal; the engine runs one process per GPU (model_runner.py:29)
+  static DevInfo cache[64];
+  static bool have[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return {-1, 0};
+  if (!have[dev]) {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return {-1, 0};
+    cache[dev].ok = (prop.major == 10) ? 1 : 0;
+    cache[dev].sms = prop.multiProcessorCount;
+    have[dev] = true;
+  }
+  return cache[dev];
+}
+
+int num_sms() {
+  const DevInfo d = query_device();
+  return d.sms > 0 ? d.sms : 148;
+}
+
+static int check_arch() {
+  const DevInfo d = query_device();
+  if (d.ok < 0) return QL_ERR_CUDA;
+  return d.ok ? QL_OK : QL_ERR_UNSUPPORTED_ARCH;
+}
+
+static bool fmt_ok(int fmt) { return fmt == QL_INT8 || fmt == QL_FP8_E4M3; }
+static bool aligned(const void* p, uintptr_t a) { return ((uintptr_t)p % a) == 0; }
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace ql
+
+using namespace ql;
+
+extern "C" {
+
+int ql_version(void) { return QL_ABI_VERSION; }
+
+const char* ql_status_string(int status) {
+  switch (status) {
+    case QL_OK: return "ok";
+    case QL_ERR_BAD_FORMAT: return "unsupported element format (expected int8 or float8_e4m3fn)";
+    case QL_ERR_BAD_SHAPE: return "unsupported shape (K % 128, K % group, group % 128 or M limit violated)";
+    case QL_ERR_MISALIGNED: return "pointer or stride not 16-byte aligned";
+    case QL_ERR_UNSUPPORTED_ARCH: return "device is not compute capability 10.x (B200, sm_100a); no fallback exists";
+    case QL_ERR_WORKSPACE: return "workspace missing or too small";
+    case QL_ERR_CUDA: return "CUDA runtime/driver call failed";
+    case QL_ERR_NULL: return "required pointer is NULL";
+    default: return "unknown status";
+  }
+}
+
+int ql_device_check(void) { return check_arch(); }
+
+int ql_quant_rows(const void* x, int64_t M, int64_t K, int64_t ldx, int fmt, void* q, float* s,
+                  ql_stream_t stream) {
+  if (!fmt_ok(fmt)) return QL_ERR_BAD_FORMAT;
+  if (M < 0 || K <= 0 || ldx < K) return QL_ERR_BAD_SHAPE;
+  if (M == 0) return QL_OK;
+  if (!x || !q || !s) return QL_ERR_NULL;
+  if (int e = check_arch()) return e;
+  return launch_quant_rows(x, M, K, ldx, fmt, q, s, (cudaStream_t)stream);
+}
+
+int ql_quant_groups(const void* w, int64_t N, int64_t K, int64_t group, int fmt, void* q,
+                    float* s, ql_stream_t stream) {
+  if (!fmt_ok(fmt)) return QL_ERR_BAD_FORMAT;
+  if (N < 0 || K <= 0 || group <= 0 || K % group != 0) return QL_ERR_BAD_SHAPE;
+  if (N == 0) return QL_OK;
+  if (!w || !q || !s) return QL_ERR_NULL;
+  if (int e = check_arch()) return e;
+  return launch_quant_groups(w, N, K, group, fmt, q, s, (cudaStream_t)stream);
+}
+
+int ql_quant_tensor(const void* x, int64_t numel, int fmt, void* q, void* scale_bf16,
+                    void* workspace, size_t workspace_bytes, ql_stream_t stream) {
+  if (!fmt_ok(fmt)) return QL_ERR_BAD_FORMAT;
+  if (numel < 0) return QL_ERR_BAD_SHAPE;
+  if (numel == 0) return QL_OK;
+  if (!x || !q || !scale_bf16) return QL_ERR_NULL;
+  if (!workspace || workspace_bytes < 4) return QL_ERR_WORKSPACE;
+  if (!aligned(workspace, 4)) return QL_ERR_MISALIGNED;
+  if (int e = check_arch()) return e;
+  return launch_quant_tensor(x, numel, fmt, q, scale_bf16, workspace, (cudaStream_t)stream);
+}
+
+static int check_gemm_common(int64_t M, int64_t N, int64_t K, int fmt, int64_t group) {
+  if (!fmt_ok(fmt)) return QL_ERR_BAD_FORMAT;
+  if (M < 0 || N < 0 || K <= 0 || K % 128 != 0) return QL_ERR_BAD_SHAPE;  // reference :328
+  if (group < 0 || (group > 0 && (group % 128 != 0 || K % group != 0))) return QL_ERR_BAD_SHAPE;
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) return QL_ERR_BAD_SHAPE;
+  return QL_OK;
+}
+
+int ql_gemm_w8a8(const void* qx, const float* sx, const void* qw, const float* sw,
+                 const void* bias, void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int fmt,
+                 int64_t group, ql_stream_t stream) {
+  if (int e = check_gemm_common(M, N, K, fmt, group)) return e;
+  if (ldy < N) return QL_ERR_BAD_SHAPE;
+  if (M == 0 || N == 0) return QL_OK;
+  if (!qx || !sx || !qw || !sw || !y) return QL_ERR_NULL;
+  if (!aligned(qx, 16) || !aligned(qw, 16)) return QL_ERR_MISALIGNED;  // TMA global address
+  if (int e = check_arch()) return e;
+  return launch_gemm(qx, sx, qw, sw, bias, y, ldy, nullptr, M, N, K, fmt, group,
+                     (cudaStream_t)stream);
+}
+
+int ql_gemm_i8_acc(const void* qx, const void* qw, int32_t* acc, int64_t M, int64_t N, int64_t K,
+                   ql_stream_t stream) {
+  if (int e = check_gemm_common(M, N, K, QL_INT8, 0)) return e;
+  if (M == 0 || N == 0) return QL_OK;
+  if (!qx || !qw || !acc) return QL_ERR_NULL;
+  if (!aligned(qx, 16) || !aligned(qw, 16)) return QL_ERR_MISALIGNED;
+  if (int e = check_arch()) return e;
+  return launch_gemm(qx, nullptr, qw, nullptr, nullptr, nullptr, N, acc, M, N, K, QL_INT8, 0,
+                     (cudaStream_t)stream);
+}
+
+int ql_gemv_w8a8(const void* x, int64_t ldx, const void* qw, const float* sw, const void* bias,
+                 void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int fmt, int64_t group,
+                 ql_stream_t stream) {
+  if (int e = check_gemm_common(M, N, K, fmt, group)) return e;
+  if (M > 16 || ldx < K || ldy < N) return QL_ERR_BAD_SHAPE;
+  if (M == 0 || N == 0) return QL_OK;
+  if (!x || !qw || !sw || !y) return QL_ERR_NULL;
+  if (!aligned(x, 16) || ldx % 8 != 0 || !aligned(qw, 16)) return QL_ERR_MISALIGNED;
+  if (int e = check_arch()) return e;
+  return launch_gemv(x, ldx, nullptr, nullptr, qw, sw, bias, y, ldy, M, N, K, fmt, group,
+                     (cudaStream_t)stream);
+}
+
+size_t ql_workspace_bytes(int64_t M, int64_t K) {
+  if (M <= 16 || K <= 0) return 0;
+  // qx [M,K] (16-byte aligned) followed by sx [M]
+  return align_up((size_t)M * (size_t)K, 256) + align_up((size_t)M * sizeof(float), 256);
+}
+
+const char* ql_linear_path(int64_t M, int64_t N, int64_t K, int64_t group) {
+  (void)N; (void)K; (void)group;
+  return M <= 16 ? "gemv_mma" : "gemm_tcgen05";
+}
+
+int ql_linear(const void* x, int64_t ldx, const void* qw, const float* sw, const void* bias,
+              void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int fmt, int64_t group,
+              void* workspace, size_t workspace_bytes, ql_stream_t stream) {
+  if (int e = check_gemm_common(M, N, K, fmt, group)) return e;
+  if (ldx < K || ldy < N) return QL_ERR_BAD_SHAPE;
+  if (M == 0 || N == 0) return QL_OK;
+  if (!x || !qw || !sw || !y) return QL_ERR_NULL;
+  if (!aligned(x, 16) || ldx % 8 != 0 || !aligned(qw, 16)) return QL_ERR_MISALIGNED;
+  if (int e = check_arch()) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (M <= 16)
+    return launch_gemv(x, ldx, nullptr, nullptr, qw, sw, bias, y, ldy, M, N, K, fmt, group, st);
+  const size_t need = ql_workspace_bytes(M, K);
+  if (workspace == nullptr || workspace_bytes < need) return QL_ERR_WORKSPACE;
+  if (!aligned(workspace, 16)) return QL_ERR_MISALIGNED;
+  uint8_t* qx = static_cast<uint8_t*>(workspace);
+  float* sx = reinterpret_cast<float*>(qx + align_up((size_t)M * (size_t)K, 256));
+  if (int e = launch_quant_rows(x, M, K, ldx, fmt, qx, sx, st)) return e;
+  return launch_gemm(qx, sx, qw, sw, bias, y, ldy, nullptr, M, N, K, fmt, group, st);
+}
+
+}  // extern "C"

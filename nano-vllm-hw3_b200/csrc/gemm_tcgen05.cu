@@ -1,0 +1,371 @@
+// W8A8 GEMM on the 5th-generation tensor cores (tcgen05) with the scale/bias epilogue fused.
+// Replaces the reference's Triton kernel _per_row_post_process_mm
+// (nanovllm/utils/quantization.py:54-144) and, for group > 0, the fp32 dequant + SGEMM of
+// per_group_matmul (:265-307).
+//
+// Orientation ("weight-stationary", swap-AB): the UMMA A operand is a 128-row tile of the
+// WEIGHT matrix qw[N,K]; the B operand is a BT-token tile of the quantised activations
+// qx[M,K] (BT = 32..256 = UMMA N).  The accumulator D[128 x BT] lives in TMEM with the weight
+// row n on the TMEM lane and the token m on the column, so in the epilogue each thread owns one
+// output feature n: its weight scale(s) sw[n] / sw[n,j] and bias[n] are per-thread scalars and
+// the bf16 stores of a warp cover 32 consecutive n of one token (64 contiguous bytes).
+//
+// Pipeline per CTA (persistent over tiles, 256 threads):
+//   warp 0 (1 lane)  TMA producer: cp.async.bulk.tensor 128-byte-swizzled tiles of qw and qx
+//                    into a STAGES-deep shared-memory ring, completion on `full` mbarriers
+//   warp 1 (1 lane)  MMA issuer: 4 x tcgen05.mma (K = 32 bytes each) per 128-byte K block,
+//                    tcgen05.commit -> `empty` (smem slot free) and `tfull` (accumulator ready)
+//   warp 2           TMEM allocator (512 columns = 2..4 accumulator buffers)
+//   warps 4-7        epilogue: tcgen05.ld 32 lanes x 32 columns -> registers -> scales -> bf16
+// Per-row mode: one accumulator per tile (all of K), double-buffered so the epilogue of tile i
+// overlaps the MMAs of tile i+1.  Per-group mode: one accumulator per 128-wide K block; the
+// epilogue warps promote each block with its weight scale into fp32 registers
+// (t = fmaf(float(P_j), sw[n,j], t)) while the tensor core fills the next buffer.
+//
+// INT8 accumulators are exact int32 (kind::i8, SASS UTCIMMA); FP8 accumulates in fp32
+// (kind::f8f6f4, SASS UTCQMMA).  Epilogue order is the reference's: (float(acc) * sx[m]) * sw[n].
+#include <cuda.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ql {
+
+struct GemmParams {
+  const float* sx;       // [M]
+  const float* sw;       // [N] or [N, G]
+  const uint16_t* bias;  // bf16 [N] or nullptr
+  uint16_t* y;           // bf16 [M, ldy]
+  int64_t ldy;
+  int32_t* acc_out;      // int32 [M, N] (OUT_ACC only)
+  int M, N, K;
+  int G;                 // scale columns (per-group) or 1
+  int kb_per_g;          // 128-byte K blocks per scale group
+  int tiles_n, tiles_m;
+};
+
+constexpr int kGemmThreads = 256;
+constexpr int kTileN = 128;   // weight rows per tile (UMMA M)
+constexpr int kBlockK = 128;  // bytes of K per pipeline stage (one 128B swizzle atom)
+constexpr int kSmemBudget = 227 * 1024;
+
+template <int BT> struct GemmCfg {
+  static constexpr int stage_a = kTileN * kBlockK;
+  static constexpr int stage_b = BT * kBlockK;
+  static constexpr int stage = stage_a + stage_b;
+  static constexpr int stages_raw = (kSmemBudget - 2048) / stage;
+  static constexpr int stages = stages_raw > 8 ? 8 : stages_raw;
+  static constexpr int nacc_raw = 512 / BT;
+  static constexpr int nacc = nacc_raw > 4 ? 4 : nacc_raw;
+  static constexpr int tmem_cols_raw = nacc * BT;
+  static constexpr int tmem_cols = tmem_cols_raw <= 32 ? 32 : tmem_cols_raw <= 64 ? 64
+                                   : tmem_cols_raw <= 128 ? 128 : tmem_cols_raw <= 256 ? 256 : 512;
+  static constexpr int smem_bytes = stages * stage + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int FMT, bool GROUPED, int BT, bool OUT_ACC>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
+            const GemmParams p) {
+  using Cfg = GemmCfg<BT>;
+  constexpr int STAGES = Cfg::stages;
+  constexpr int NACC = Cfg::nacc;
+  static_assert(!(GROUPED && BT > 128), "per-group epilogue keeps BT fp32 sums in registers");
+  static_assert(!(OUT_ACC && (GROUPED || FMT != QL_INT8)), "raw accumulators: int8 per-row only");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::stage);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + NACC;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + NACC);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_w);
+    tma_prefetch_desc(&tm_x);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < NACC; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 4);  // one arrive per epilogue warp
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, Cfg::tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_kb = p.K / kBlockK;
+  const int total_tiles = p.tiles_n * p.tiles_m;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int tn = tile % p.tiles_n, tm = tile / p.tiles_n;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::stage;
+          mbar_expect_tx(&full_bar[stage], Cfg::stage);
+          tma_load_2d(sa, &tm_w, &full_bar[stage], kb * kBlockK, tn * kTileN, kEvictNormal);
+          tma_load_2d(sa + Cfg::stage_a, &tm_x, &full_bar[stage], kb * kBlockK, tm * BT,
+                      kEvictNormal);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc<FMT>(kTileN, BT);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        if constexpr (!GROUPED) {
+          mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+          tc_fence_after();
+        }
+        for (int kb = 0; kb < num_kb; ++kb) {
+          if constexpr (GROUPED) {
+            mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+            tc_fence_after();
+          }
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * Cfg::stage);
+          const uint64_t a_desc = make_sw128_kmajor_desc(sa);
+          const uint64_t b_desc = make_sw128_kmajor_desc(sa + Cfg::stage_a);
+          const uint32_t d_tmem = tmem_base + acc * BT;
+#pragma unroll
+          for (int k = 0; k < kBlockK / 32; ++k) {
+            const uint32_t accumulate = GROUPED ? (k > 0) : (kb > 0 || k > 0);
+            // +32 bytes of K inside the swizzle atom = +2 in the (addr >> 4) field
+            if constexpr (FMT == QL_INT8)
+              mma_i8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, accumulate);
+            else
+              mma_f8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, accumulate);
+          }
+          tc_commit(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if constexpr (GROUPED) {
+            tc_commit(&tfull_bar[acc]);
+            if (++acc == NACC) { acc = 0; acc_phase ^= 1; }
+          }
+        }
+        if constexpr (!GROUPED) {
+          tc_commit(&tfull_bar[acc]);
+          if (++acc == NACC) { acc = 0; acc_phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (TMEM -> registers -> global) =====================
+    const int q = warp - 4;  // TMEM lane quarter: this warp reads lanes [32q, 32q+32)
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int tn = tile % p.tiles_n, tm = tile / p.tiles_n;
+      const int n = tn * kTileN + q * 32 + lane;
+      const bool n_ok = n < p.N;
+      const int m0 = tm * BT;
+      const float biasv = (p.bias != nullptr && n_ok) ? bf16_lo(p.bias[n]) : 0.0f;
+
+      if constexpr (!GROUPED) {
+        const float swn = (!OUT_ACC && n_ok) ? __ldg(p.sw + n) : 0.0f;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BT / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld32(lane_addr + acc * BT + c * 32, r);
+          const int mc = m0 + c * 32;
+          const float sx_l = (!OUT_ACC && mc + lane < p.M) ? __ldg(p.sx + mc + lane) : 0.0f;
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int m = mc + i;
+            if constexpr (OUT_ACC) {
+              if (m < p.M && n_ok) p.acc_out[(int64_t)m * p.N + n] = (int32_t)r[i];
+            } else {
+              const float sxm = __shfl_sync(0xffffffffu, sx_l, i);
+              const float a = FMT == QL_INT8 ? __int2float_rn((int)r[i]) : __uint_as_float(r[i]);
+              float v = __fmul_rn(__fmul_rn(a, sxm), swn);  // (acc * sa) * sb
+              if (p.bias != nullptr) v = __fadd_rn(v, biasv);
+              if (m < p.M && n_ok) p.y[(int64_t)m * p.ldy + n] = f2bf(v);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        if (++acc == NACC) { acc = 0; acc_phase ^= 1; }
+      } else {
+        float t[BT];
+#pragma unroll
+        for (int i = 0; i < BT; ++i) t[i] = 0.0f;
+        const float* swrow = p.sw + (int64_t)(n_ok ? n : 0) * p.G;
+        float sc = __ldg(swrow);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int nxt = (kb + 1 < num_kb) ? (kb + 1) / p.kb_per_g : 0;
+          const float sc_next = __ldg(swrow + nxt);
+          mbar_wait(&tfull_bar[acc], acc_phase);
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < BT / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(lane_addr + acc * BT + c * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const float a = FMT == QL_INT8 ? __int2float_rn((int)r[i]) : __uint_as_float(r[i]);
+              t[c * 32 + i] = fmaf(a, sc, t[c * 32 + i]);
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+          if (++acc == NACC) { acc = 0; acc_phase ^= 1; }
+          sc = sc_next;
+        }
+#pragma unroll
+        for (int c = 0; c < BT / 32; ++c) {
+          const int mc = m0 + c * 32;
+          const float sx_l = (mc + lane < p.M) ? __ldg(p.sx + mc + lane) : 0.0f;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int m = mc + i;
+            const float sxm = __shfl_sync(0xffffffffu, sx_l, i);
+            float v = __fmul_rn(t[c * 32 + i], sxm);
+            if (p.bias != nullptr) v = __fadd_rn(v, biasv);
+            if (m < p.M && n_ok) p.y[(int64_t)m * p.ldy + n] = f2bf(v);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, Cfg::tmem_cols);
+}
+
+// ------------------------------------------------------------------ host side
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// 2-D uint8 tensor [rows, K] (K contiguous), box = {128 K-bytes, box_rows}, 128B swizzle,
+// out-of-bounds rows read as zero.
+static bool make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t K, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)K};
+  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), gdim, gstride, box,
+            estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int FMT, bool GROUPED, int BT, bool OUT_ACC>
+static int launch_cfg(const void* qx, const void* qw, GemmParams p, cudaStream_t st) {
+  using Cfg = GemmCfg<BT>;
+  auto kern = gemm_kernel<FMT, GROUPED, BT, OUT_ACC>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes) !=
+        cudaSuccess)
+      return QL_ERR_CUDA;
+    attr_set = true;
+  }
+  CUtensorMap tm_w, tm_x;
+  if (!make_tmap(&tm_w, qw, p.N, p.K, kTileN) || !make_tmap(&tm_x, qx, p.M, p.K, BT))
+    return QL_ERR_CUDA;
+  p.tiles_n = (p.N + kTileN - 1) / kTileN;
+  p.tiles_m = (p.M + BT - 1) / BT;
+  const int64_t tiles = (int64_t)p.tiles_n * p.tiles_m;
+  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  kern<<<grid, kGemmThreads, Cfg::smem_bytes, st>>>(tm_w, tm_x, p);
+  return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
+}
+
+// Token-tile width: smallest tile covering M for M <= 128; above that the width with the
+// fewest tensor-core cycles over whole waves (tile time ~ BT per K block).
+static int pick_bt(int64_t M, int64_t N, bool grouped) {
+  if (M <= 32) return 32;
+  if (M <= 64) return 64;
+  if (M <= 128 || grouped) return 128;
+  const int64_t tn = (N + kTileN - 1) / kTileN;
+  const int sms = num_sms();
+  const int64_t c128 = ((tn * ((M + 127) / 128) + sms - 1) / sms) * 128;
+  const int64_t c256 = ((tn * ((M + 255) / 256) + sms - 1) / sms) * 256;
+  return c128 < c256 ? 128 : 256;
+}
+
+template <int FMT, bool GROUPED, bool OUT_ACC>
+static int launch_bt(const void* qx, const void* qw, const GemmParams& p, cudaStream_t st) {
+  switch (pick_bt(p.M, p.N, GROUPED)) {
+    case 32: return launch_cfg<FMT, GROUPED, 32, OUT_ACC>(qx, qw, p, st);
+    case 64: return launch_cfg<FMT, GROUPED, 64, OUT_ACC>(qx, qw, p, st);
+    case 128: return launch_cfg<FMT, GROUPED, 128, OUT_ACC>(qx, qw, p, st);
+    default:
+      if constexpr (GROUPED) return QL_ERR_BAD_SHAPE;
+      else return launch_cfg<FMT, GROUPED, 256, OUT_ACC>(qx, qw, p, st);
+  }
+}
+
+int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw,
+                const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
+                int64_t K, int fmt, int64_t group, cudaStream_t st) {
+  if (M == 0 || N == 0) return QL_OK;
+  GemmParams p;
+  p.sx = sx; p.sw = sw;
+  p.bias = static_cast<const uint16_t*>(bias);
+  p.y = static_cast<uint16_t*>(y);
+  p.ldy = ldy;
+  p.acc_out = out_acc;
+  p.M = (int)M; p.N = (int)N; p.K = (int)K;
+  p.G = group > 0 ? (int)(K / group) : 1;
+  p.kb_per_g = group > 0 ? (int)(group / kBlockK) : 1;
+  p.tiles_n = p.tiles_m = 0;
+  if (out_acc != nullptr) return launch_bt<QL_INT8, false, true>(qx, qw, p, st);
+  if (fmt == QL_INT8)
+    return group > 0 ? launch_bt<QL_INT8, true, false>(qx, qw, p, st)
+                     : launch_bt<QL_INT8, false, false>(qx, qw, p, st);
+  return group > 0 ? launch_bt<QL_FP8_E4M3, true, false>(qx, qw, p, st)
+                   : launch_bt<QL_FP8_E4M3, false, false>(qx, qw, p, st);
+}
+
+}  // namespace ql

@@ -1,0 +1,30 @@
+// Internal launcher declarations shared by the translation units of libqlinear_b200.so.
+// The public surface is include/qlinear_b200.h; these take validated arguments.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ql {
+
+int launch_quant_rows(const void* x, int64_t M, int64_t K, int64_t ldx, int fmt, void* q,
+                      float* s, cudaStream_t st);
+int launch_quant_groups(const void* w, int64_t N, int64_t K, int64_t g, int fmt, void* q,
+                        float* s, cudaStream_t st);
+int launch_quant_tensor(const void* x, int64_t numel, int fmt, void* q, void* scale_bf16,
+                        void* ws, cudaStream_t st);
+
+// Fused quantise + GEMV for M <= 16.  Exactly one of (x) or (qx_pre, sx_pre) is used:
+// x != nullptr quantises the activations inside the kernel.
+int launch_gemv(const void* x, int64_t ldx, const void* qx_pre, const float* sx_pre,
+                const void* qw, const float* sw, const void* bias, void* y, int64_t ldy,
+                int64_t M, int64_t N, int64_t K, int fmt, int64_t group, cudaStream_t st);
+
+// tcgen05 GEMM.  out_acc != nullptr stores raw int32 accumulators (INT8, per-row only).
+int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw,
+                const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
+                int64_t K, int fmt, int64_t group, cudaStream_t st);
+
+int num_sms();
+
+}  // namespace ql

@@ -1,0 +1,226 @@
+"""ctypes binding of libqlinear_b200.so (C ABI: include/qlinear_b200.h) + the torch glue.
+
+This is the "thin torch extension" of the quantized-linear path: torch owns every tensor and
+the stream, the library gets raw device pointers, sizes and ``cudaStream_t``.  Argument
+checks raise ``AssertionError`` where the reference asserts (nanovllm/utils/quantization.py
+:151-152, :203-205, :328) and ``RuntimeError`` for everything the library itself reports.
+
+There is NO fallback: if the shared library is missing or the device is not a B200
+(compute capability 10.x) the first call raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_lib", "libqlinear_b200.so")
+
+QL_INT8, QL_FP8_E4M3 = 0, 1
+QL_ABI_VERSION = 2
+_FMT = {torch.int8: QL_INT8, torch.float8_e4m3fn: QL_FP8_E4M3}
+
+_c_i64, _c_int, _c_vp, _c_sz = ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
+
+# name -> (restype, argtypes); mirrors include/qlinear_b200.h one to one
+SIGNATURES = {
+    "ql_version": (_c_int, []),
+    "ql_status_string": (ctypes.c_char_p, [_c_int]),
+    "ql_device_check": (_c_int, []),
+    "ql_quant_rows": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
+    "ql_quant_groups": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
+    "ql_quant_tensor": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
+    "ql_gemm_w8a8": (_c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64,
+                              _c_i64, _c_int, _c_i64, _c_vp]),
+    "ql_gemm_i8_acc": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_vp]),
+    "ql_gemv_w8a8": (_c_int, [_c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64,
+                              _c_i64, _c_int, _c_i64, _c_vp]),
+    "ql_linear": (_c_int, [_c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64,
+                           _c_i64, _c_int, _c_i64, _c_vp, _c_sz, _c_vp]),
+    "ql_workspace_bytes": (_c_sz, [_c_i64, _c_i64]),
+    "ql_linear_path": (ctypes.c_char_p, [_c_i64, _c_i64, _c_i64, _c_i64]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen the library (once).  Raises RuntimeError when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python nano-vllm-hw3_b200/build.py` "
+                "(nvcc, sm_100a).  The quantized-linear path has no CPU/Triton fallback.")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        if lib.ql_version() != QL_ABI_VERSION:
+            raise RuntimeError(f"libqlinear_b200.so ABI {lib.ql_version()} != binding {QL_ABI_VERSION}")
+        _lib = lib
+    return _lib
+
+
+def _check(status: int):
+    if status != 0:
+        raise RuntimeError(f"qlinear_b200: {load().ql_status_string(status).decode()} (status {status})")
+
+
+def fmt_of(dtype: torch.dtype) -> int:
+    assert dtype in [torch.int8, torch.float8_e4m3fn]      # reference quantization.py:151,203,353
+    return _FMT[dtype]
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _cuda_rowmajor(t: torch.Tensor, what: str):
+    if not t.is_cuda:
+        raise RuntimeError(f"qlinear_b200: {what} must be a CUDA tensor (no CPU path exists)")
+    assert t.stride(-1) == 1, f"{what} must be contiguous along its last dimension"
+
+
+# ------------------------------------------------------------------------------ entry points
+
+@torch.no_grad()
+def quant_rows(x: torch.Tensor, dtype: torch.dtype):
+    """ql_quant_rows: x bf16 [M,K] -> (q dtype [M,K], s fp32 [M])."""
+    fmt = fmt_of(dtype)
+    assert x.dim() == 2                                      # reference :152
+    assert x.dtype == torch.bfloat16, "activations/weights are bf16 (reference default dtype)"
+    _cuda_rowmajor(x, "x")
+    M, K = x.shape
+    q = torch.empty((M, K), dtype=dtype, device=x.device)
+    s = torch.empty((M,), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _check(load().ql_quant_rows(_ptr(x), M, K, x.stride(0) if M > 1 else K, fmt, _ptr(q),
+                                    _ptr(s), _stream(x)))
+    return q, s
+
+
+@torch.no_grad()
+def quant_groups(w: torch.Tensor, group_size: int, dtype: torch.dtype):
+    """ql_quant_groups: w bf16 [N,K] -> (q dtype [N,K], s fp32 [N, K/group_size])."""
+    fmt = fmt_of(dtype)
+    assert w.dim() == 2                                      # reference :204
+    assert w.size(1) % group_size == 0, \
+        f"K dim ({w.size(1)}) must be divisible by group_size ({group_size})"   # reference :205
+    assert w.dtype == torch.bfloat16
+    w = w.contiguous()
+    _cuda_rowmajor(w, "w")
+    N, K = w.shape
+    q = torch.empty((N, K), dtype=dtype, device=w.device)
+    s = torch.empty((N, K // group_size), dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        _check(load().ql_quant_groups(_ptr(w), N, K, group_size, fmt, _ptr(q), _ptr(s), _stream(w)))
+    return q, s
+
+
+@torch.no_grad()
+def quant_tensor(x: torch.Tensor, dtype: torch.dtype):
+    """ql_quant_tensor: x bf16 (any shape) -> (q dtype like x, scale 0-dim bf16), reference :166-191."""
+    fmt = fmt_of(dtype)
+    assert x.dtype == torch.bfloat16
+    x = x.contiguous()
+    _cuda_rowmajor(x, "x")
+    q = torch.empty(x.shape, dtype=dtype, device=x.device)
+    scale = torch.empty((), dtype=torch.bfloat16, device=x.device)
+    ws = torch.empty((1024,), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _check(load().ql_quant_tensor(_ptr(x), x.numel(), fmt, _ptr(q), _ptr(scale), _ptr(ws),
+                                      ws.numel() * 4, _stream(x)))
+    return q, scale
+
+
+def _prep_linear(x, qw, sw, bias, group_size):
+    assert x.dtype == torch.bfloat16
+    _cuda_rowmajor(x, "x")
+    K = x.shape[-1]
+    N = qw.shape[0]
+    assert qw.dim() == 2 and qw.shape[1] == K and qw.is_contiguous()
+    assert K % 128 == 0, f"K({K}) must be multiple of BLK_K(128)"          # reference :328
+    assert sw.dtype == torch.float32 and sw.is_contiguous()
+    if group_size:
+        assert K % group_size == 0
+        assert tuple(sw.shape) == (N, K // group_size)
+    else:
+        assert sw.numel() == N
+    if bias is not None:
+        assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
+    y_shape = list(x.shape[:-1]) + [N]
+    x2 = x.reshape(-1, K)                                    # reference :322 (view when possible)
+    if x2.stride(-1) != 1 or (x2.shape[0] > 1 and x2.stride(0) % 8 != 0) or x2.data_ptr() % 16:
+        x2 = x2.contiguous()
+    return x2, y_shape, N, K
+
+
+@torch.no_grad()
+def linear(x, qw, sw, bias, dtype, group_size: int = 0, out: torch.Tensor | None = None):
+    """ql_linear: one whole quantized linear, y = bf16[..., N].  group_size 0 = per-row scales."""
+    fmt = fmt_of(dtype)
+    assert qw.dtype == dtype
+    x2, y_shape, N, K = _prep_linear(x, qw, sw, bias, group_size)
+    M = x2.shape[0]
+    y = out if out is not None else torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    lib = load()
+    nbytes = lib.ql_workspace_bytes(M, K)
+    ws = torch.empty((nbytes,), dtype=torch.uint8, device=x.device) if nbytes else None
+    with torch.cuda.device(x.device):
+        _check(lib.ql_linear(_ptr(x2), x2.stride(0) if M > 1 else K, _ptr(qw), _ptr(sw), _ptr(bias),
+                             _ptr(y), y.stride(0) if M > 1 else N, M, N, K, fmt, group_size,
+                             _ptr(ws), nbytes, _stream(x)))
+    return y.view(y_shape) if out is None else out
+
+
+@torch.no_grad()
+def gemm_w8a8(qx, sx, qw, sw, bias, dtype, group_size: int = 0):
+    """ql_gemm_w8a8 on pre-quantised activations (tcgen05 path regardless of M)."""
+    fmt = fmt_of(dtype)
+    assert qx.dtype == dtype and qw.dtype == dtype and qx.is_contiguous() and qw.is_contiguous()
+    M, K = qx.shape
+    N = qw.shape[0]
+    assert K % 128 == 0, f"K({K}) must be multiple of BLK_K(128)"
+    y = torch.empty((M, N), dtype=torch.bfloat16, device=qx.device)
+    with torch.cuda.device(qx.device):
+        _check(load().ql_gemm_w8a8(_ptr(qx), _ptr(sx), _ptr(qw), _ptr(sw), _ptr(bias), _ptr(y), N,
+                                   M, N, K, fmt, group_size, _stream(qx)))
+    return y
+
+
+@torch.no_grad()
+def gemm_i8_acc(qx, qw):
+    """ql_gemm_i8_acc: raw int32 accumulators of the tcgen05 INT8 kernel (parity entry point)."""
+    assert qx.dtype == torch.int8 and qw.dtype == torch.int8
+    assert qx.is_contiguous() and qw.is_contiguous()
+    M, K = qx.shape
+    N = qw.shape[0]
+    assert K % 128 == 0
+    acc = torch.empty((M, N), dtype=torch.int32, device=qx.device)
+    with torch.cuda.device(qx.device):
+        _check(load().ql_gemm_i8_acc(_ptr(qx), _ptr(qw), _ptr(acc), M, N, K, _stream(qx)))
+    return acc
+
+
+@torch.no_grad()
+def gemv_w8a8(x, qw, sw, bias, dtype, group_size: int = 0):
+    """ql_gemv_w8a8: fused quantise + GEMV, M <= 16."""
+    fmt = fmt_of(dtype)
+    x2, y_shape, N, K = _prep_linear(x, qw, sw, bias, group_size)
+    M = x2.shape[0]
+    y = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    with torch.cuda.device(x.device):
+        _check(load().ql_gemv_w8a8(_ptr(x2), x2.stride(0) if M > 1 else K, _ptr(qw), _ptr(sw),
+                                   _ptr(bias), _ptr(y), N, M, N, K, fmt, group_size, _stream(x)))
+    return y.view(y_shape)
+
+
+def linear_path(M: int, N: int, K: int, group_size: int = 0) -> str:
+    return load().ql_linear_path(M, N, K, group_size).decode()

@@ -1,0 +1,411 @@
+"""GPU parity tests proper: the sm_100a CUDA path (through the C ABI via nanovllm._ext)
+against the CPU oracle (oracle/, test infrastructure) and the committed reference goldens.
+
+Bars:
+  L0 quantisers .......... bit-exact q and s
+  L1 INT8 accumulators ... bit-exact int32 (ql_gemm_i8_acc)
+  L2 scaled bf16 output .. INT8 per-row / per-group GEMM: bit-exact vs the oracle;
+                           FP8 (fp32 accumulation order differs) and the split-K GEMV in
+                           per-group mode: |dy| <= FP_TOL_ULP bf16 ulp of max|y|, rel-L2 <= FP_TOL_L2
+  L3 reference thresholds  max|y - x@w.T| / max|x@w.T| < 0.08 (per-row, quantization.py:549-553)
+                           and < 0.1 (per-group / per-tensor, :583, :615)
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+FP_TOL_ULP = 1.0      # of max|y| (one bf16 ulp at the largest magnitude = 2^-7 relative)
+FP_TOL_L2 = 2e-3
+
+DT = {"i8": torch.int8, "f8": torch.float8_e4m3fn}
+FMT = {"i8": orc.INT8, "f8": orc.FP8}
+
+
+@pytest.fixture(scope="module")
+def ext():
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    from nanovllm import _ext
+    assert _ext.load().ql_device_check() == 0, "device is not sm_100"
+    return _ext
+
+
+def dev(a: np.ndarray, dtype) -> torch.Tensor:
+    return orc.n2t(a, dtype).cuda()
+
+
+def bits(t: torch.Tensor) -> np.ndarray:
+    return orc.t2n(t)
+
+
+def rand_bf16(shape, seed, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(torch.bfloat16)
+
+
+def bf16_ulp_diff(a_u16, b_u16):
+    def key(u):
+        u = u.astype(np.int32)
+        return np.where(u & 0x8000, 0x8000 - u, u)
+    return np.abs(key(a_u16) - key(b_u16))
+
+
+def assert_close_fp(y_u16, ref_u16, what=""):
+    y, r = orc.bf16_decode(y_u16).astype(np.float64), orc.bf16_decode(ref_u16).astype(np.float64)
+    amax = np.abs(r).max()
+    if amax == 0:
+        assert np.abs(y).max() == 0
+        return
+    ulp_at_max = 2.0 ** (np.floor(np.log2(amax)) - 7)
+    err = np.abs(y - r).max()
+    assert err <= FP_TOL_ULP * ulp_at_max, f"{what}: max err {err} > {FP_TOL_ULP} ulp(max)={ulp_at_max}"
+    l2 = np.sqrt(((y - r) ** 2).sum() / max((r ** 2).sum(), 1e-30))
+    assert l2 <= FP_TOL_L2, f"{what}: rel-L2 {l2}"
+
+
+# ------------------------------------------------------------------ L0: quantisers
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+def test_quant_rows_golden(ext, golden, dn, tag):
+    for src, qk, sk in (("x", "qx", "sx"), ("w", "qw", "sw")):
+        x = golden[f"pr_{tag}_{src}"]
+        q, s = ext.quant_rows(dev(x, torch.bfloat16), DT[dn])
+        qo, so = orc.quant_rows(x, FMT[dn])
+        assert np.array_equal(bits(s), so)
+        assert np.array_equal(bits(q), qo)
+        assert np.array_equal(bits(s), golden[f"pr_{tag}_{dn}_{sk}"])
+        if dn == "i8":      # the interpreter's fp8 cast is not the hardware cast (see test_oracle_golden)
+            assert np.array_equal(bits(q), golden[f"pr_{tag}_{dn}_{qk}"])
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("M,K", [(1, 1024), (7, 2048), (33, 3072), (16, 4096), (5, 12288),
+                                 (3, 136), (2, 100), (4096, 1024), (1, 8)])
+def test_quant_rows_shapes(ext, dn, M, K):
+    x = rand_bf16((M, K), 100 + M + K)
+    if M > 2:
+        x[1].zero_()
+        x[2] *= 1e-3
+        x[0, 0] = 3.0e4
+    q, s = ext.quant_rows(x.cuda(), DT[dn])
+    qo, so = orc.quant_rows(bits(x), FMT[dn])
+    assert np.array_equal(bits(s), so)
+    assert np.array_equal(bits(q), qo)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+def test_quant_rows_strided_and_empty(ext, dn):
+    big = rand_bf16((9, 1024 + 64), 5).cuda()
+    x = big[:, 32:32 + 1024]                      # row stride 1088, 64-byte offset
+    q, s = ext.quant_rows(x, DT[dn])
+    qo, so = orc.quant_rows(bits(x.contiguous()), FMT[dn])
+    assert np.array_equal(bits(q), qo) and np.array_equal(bits(s), so)
+    x2 = big[:, 3:3 + 1024]                       # misaligned -> scalar kernel
+    q, s = ext.quant_rows(x2, DT[dn])
+    qo, so = orc.quant_rows(bits(x2.contiguous()), FMT[dn])
+    assert np.array_equal(bits(q), qo) and np.array_equal(bits(s), so)
+    q, s = ext.quant_rows(torch.empty((0, 256), dtype=torch.bfloat16, device="cuda"), DT[dn])
+    assert q.shape == (0, 256) and s.shape == (0,)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("tag", ["a", "b"])
+@pytest.mark.parametrize("gs", [64, 128, "K"])
+def test_quant_groups_golden(ext, golden, dn, tag, gs):
+    w = golden[f"pg_{tag}_w"]
+    g = w.shape[1] if gs == "K" else gs
+    q, s = ext.quant_groups(dev(w, torch.bfloat16), g, DT[dn])
+    assert np.array_equal(bits(q), golden[f"pg_{tag}_{dn}_g{g}_q"])
+    assert np.array_equal(bits(s), golden[f"pg_{tag}_{dn}_g{g}_s"])
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("N,K,g", [(1024, 3072, 128), (96, 2048, 256), (40, 1024, 32), (7, 512, 512)])
+def test_quant_groups_shapes(ext, dn, N, K, g):
+    w = rand_bf16((N, K), N + K + g, 0.02)
+    w[N // 2].zero_()
+    q, s = ext.quant_groups(w.cuda(), g, DT[dn])
+    qo, so = orc.quant_groups(bits(w), g, FMT[dn])
+    assert np.array_equal(bits(s), so) and np.array_equal(bits(q), qo)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+def test_quant_tensor_golden(ext, golden, dn):
+    q, sc = ext.quant_tensor(dev(golden["pt_w"], torch.bfloat16), DT[dn])
+    assert sc.dtype == torch.bfloat16 and sc.dim() == 0
+    assert float(sc) == float(golden[f"pt_{dn}_s"][0])
+    assert np.array_equal(bits(q), golden[f"pt_{dn}_q"])
+
+
+# ------------------------------------------------------------------ L1: int32 accumulators
+
+def rand_i8(shape, seed):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randint(-127, 128, shape, generator=g, dtype=torch.int8)
+
+
+@pytest.mark.parametrize("M,N,K", [
+    (1, 8, 128), (5, 136, 256), (17, 24, 384), (32, 128, 128), (33, 1024, 1024), (64, 256, 512),
+    (100, 130, 1152), (128, 128, 2048), (130, 24, 128), (256, 512, 1024), (300, 1000, 640),
+    (1000, 136, 256), (513, 4096, 1024)])
+def test_gemm_i8_acc_bit_exact(ext, M, N, K):
+    qx, qw = rand_i8((M, K), M * 7 + K), rand_i8((N, K), N * 3 + K)
+    if M > 1:
+        qx[-1] = 127
+        qw[-1] = -127           # extreme accumulators: K * 127^2
+    acc = ext.gemm_i8_acc(qx.cuda(), qw.cuda())
+    ref = orc.gemm_i8_acc(qx.numpy(), qw.numpy())
+    assert np.array_equal(acc.cpu().numpy(), ref)
+
+
+# ------------------------------------------------------------------ L2: scaled outputs
+
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+def test_gemm_rows_golden(ext, golden, tag, dn):
+    """Reference Triton fixtures (TRITON_INTERPRET) -> tcgen05 GEMM on their qx/qw/sx/sw."""
+    p = f"pr_{tag}_{dn}_"
+    qx, qw = golden[p + "qx"], golden[p + "qw"]
+    K = qx.shape[1]
+    y = ext.gemm_w8a8(dev(qx, DT[dn]), dev(golden[p + "sx"], torch.float32), dev(qw, DT[dn]),
+                      dev(golden[p + "sw"], torch.float32), None, DT[dn])
+    yo, yf = orc.gemm_rows(qx, golden[p + "sx"], qw, golden[p + "sw"], None, FMT[dn], return_f32=True)
+    if dn == "i8":
+        assert np.array_equal(bits(y), yo)
+        # the interpreter truncates fp32->bf16; hardware rounds to nearest even (<= 1 ulp apart)
+        assert bf16_ulp_diff(bits(y), golden[p + "y"]).max() <= 1
+    else:
+        assert_close_fp(bits(y), yo, p)
+    assert K % 128 == 0
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("bias", [False, True])
+@pytest.mark.parametrize("M,N,K", [(17, 136, 256), (64, 1024, 1024), (128, 4096, 1024),
+                                   (200, 1024, 2048), (257, 520, 384), (1024, 256, 128)])
+def test_gemm_rows_vs_oracle(ext, dn, bias, M, N, K):
+    x, w = rand_bf16((M, K), M + N), rand_bf16((N, K), K + N, 0.02)
+    b = rand_bf16((N,), 9) if bias else None
+    qx, sx = orc.quant_rows(bits(x), FMT[dn])
+    qw, sw = orc.quant_rows(bits(w), FMT[dn])
+    y = ext.gemm_w8a8(dev(qx, DT[dn]), dev(sx, torch.float32), dev(qw, DT[dn]), dev(sw, torch.float32),
+                      None if b is None else b.cuda(), DT[dn])
+    yo = orc.gemm_rows(qx, sx, qw, sw, None if b is None else bits(b), FMT[dn])
+    if dn == "i8":
+        assert np.array_equal(bits(y), yo)
+    else:
+        assert_close_fp(bits(y), yo)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("g", [128, 256])
+@pytest.mark.parametrize("M,N,K", [(17, 136, 256), (64, 512, 1024), (128, 1024, 3072), (300, 264, 512)])
+def test_gemm_groups_vs_oracle(ext, dn, g, M, N, K):
+    x, w = rand_bf16((M, K), M + N + g), rand_bf16((N, K), K + N + g, 0.02)
+    w[3, :g] *= 30.0
+    b = rand_bf16((N,), 11)
+    qx, sx = orc.quant_rows(bits(x), FMT[dn])
+    qw, sw = orc.quant_groups(bits(w), g, FMT[dn])
+    y = ext.gemm_w8a8(dev(qx, DT[dn]), dev(sx, torch.float32), dev(qw, DT[dn]), dev(sw, torch.float32),
+                      b.cuda(), DT[dn], g)
+    yo = orc.gemm_groups(qx, sx, qw, sw, bits(b), g, FMT[dn])
+    if dn == "i8":
+        assert np.array_equal(bits(y), yo)
+    else:
+        assert_close_fp(bits(y), yo)
+
+
+# ------------------------------------------------------------------ decode regime: fused GEMV
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("M", [1, 2, 5, 8, 9, 16])
+@pytest.mark.parametrize("N,K", [(4096, 1024), (1024, 2048), (6144, 1024), (1024, 3072), (136, 256),
+                                 (8, 128), (12, 4096)])
+def test_gemv_rows(ext, dn, M, N, K):
+    x, w = rand_bf16((M, K), M + N + 1), rand_bf16((N, K), K + N + 1, 0.02)
+    b = rand_bf16((N,), 13) if (M % 2) else None
+    qw, sw = orc.quant_rows(bits(w), FMT[dn])
+    y = ext.gemv_w8a8(x.cuda(), dev(qw, DT[dn]), dev(sw, torch.float32),
+                      None if b is None else b.cuda(), DT[dn])
+    qx, sx = orc.quant_rows(bits(x), FMT[dn])
+    yo = orc.gemm_rows(qx, sx, qw, sw, None if b is None else bits(b), FMT[dn])
+    if dn == "i8":
+        assert np.array_equal(bits(y), yo)          # exact int32 sums, same epilogue order
+    else:
+        assert_close_fp(bits(y), yo)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("M", [1, 7, 16])
+@pytest.mark.parametrize("N,K,g", [(4096, 1024, 128), (1024, 3072, 128), (520, 512, 256), (6144, 1024, 1024)])
+def test_gemv_groups(ext, dn, M, N, K, g):
+    x, w = rand_bf16((M, K), M + N + 2), rand_bf16((N, K), K + N + 2, 0.02)
+    w[1, :g] *= 25.0
+    qw, sw = orc.quant_groups(bits(w), g, FMT[dn])
+    y = ext.gemv_w8a8(x.cuda(), dev(qw, DT[dn]), dev(sw, torch.float32), None, DT[dn], g)
+    qx, sx = orc.quant_rows(bits(x), FMT[dn])
+    yo = orc.gemm_groups(qx, sx, qw, sw, None, g, FMT[dn])
+    assert_close_fp(bits(y), yo)                     # split-K changes the fp32 summation order
+
+
+# ------------------------------------------------------------------ reference-style API tests
+
+def _rel_err(y, y_ref):
+    return float((y.float() - y_ref.float()).abs().max() / y_ref.float().abs().max())
+
+
+@pytest.mark.parametrize("dtype", [torch.int8, torch.float8_e4m3fn])
+@pytest.mark.parametrize("M,N,K", [(1, 1536, 1536), (10, 1536, 1536), (4096, 4096, 4096)])
+def test_quant_mm(ext, dtype, M, N, K):
+    """The reference's own test_quant_mm (quantization.py:527-555), seeded, with its threshold."""
+    from nanovllm.utils.quantization import per_row_matmul, per_row_quant
+    torch.manual_seed(M + N)
+    x = torch.randn(M, K, dtype=torch.bfloat16, device="cuda")
+    w = torch.randn(N, K, dtype=torch.bfloat16, device="cuda")
+    b = torch.randn(N, dtype=torch.bfloat16, device="cuda")
+    qw, sw = per_row_quant(w, dtype)
+    assert qw.dtype == dtype and sw.dtype == torch.float32 and sw.shape == (N,)
+    y = per_row_matmul(x, qw, sw, b, dtype)
+    y_ref = x @ w.T + b
+    assert y.shape == y_ref.shape and y.dtype == torch.bfloat16
+    assert _rel_err(y, y_ref) < 0.08
+    y3 = per_row_matmul(x.view(1, M, K), qw, sw, None, dtype)       # 3-D input (test_ppl.py shape)
+    assert y3.shape == (1, M, N)
+
+
+@pytest.mark.parametrize("dtype", [torch.int8, torch.float8_e4m3fn])
+@pytest.mark.parametrize("g", [128, 256])
+@pytest.mark.parametrize("M,N,K", [(1, 512, 512), (10, 1024, 1024), (100, 1024, 1024)])
+def test_group_quant_mm(ext, dtype, g, M, N, K):
+    """test_group_quant_mm (quantization.py:588-619) against bf16 matmul AND the reference's
+    weight-only dequant+matmul (oracle restatement), threshold < 0.1 as the reference."""
+    from nanovllm.utils.quantization import per_group_matmul, per_group_quant
+    torch.manual_seed(M + N + g)
+    x = torch.randn(M, K, dtype=torch.bfloat16, device="cuda")
+    w = torch.randn(N, K, dtype=torch.bfloat16, device="cuda")
+    b = torch.randn(N, dtype=torch.bfloat16, device="cuda")
+    qw, sw = per_group_quant(w, g, dtype)
+    assert sw.shape == (N, K // g)
+    y = per_group_matmul(x, qw, sw, b, g, dtype)
+    assert _rel_err(y, x @ w.T + b) < 0.1
+    y_ref = orc.ref_per_group_matmul(x.cpu(), qw.cpu(), sw.cpu(), b.cpu(), g, dtype)
+    assert _rel_err(y.cpu(), y_ref) < 0.1
+
+
+@pytest.mark.parametrize("dtype", [torch.int8, torch.float8_e4m3fn])
+@pytest.mark.parametrize("M,N,K", [(1, 512, 512), (10, 1024, 1024), (32, 2048, 2048)])
+def test_tensor_quant_mm(ext, dtype, M, N, K):
+    """test_tensor_quant_mm (quantization.py:558-585), threshold < 0.1."""
+    from nanovllm.utils.quantization import per_tensor_matmul, per_tensor_quant
+    torch.manual_seed(M + N)
+    x = torch.randn(M, K, dtype=torch.bfloat16, device="cuda")
+    w = torch.randn(N, K, dtype=torch.bfloat16, device="cuda")
+    b = torch.randn(N, dtype=torch.bfloat16, device="cuda")
+    qw, sw = per_tensor_quant(w, dtype)
+    y = per_tensor_matmul(x, qw, sw, b, dtype)
+    assert _rel_err(y, x @ w.T + b) < 0.1
+
+
+def test_assertions_like_reference(ext):
+    from nanovllm.utils.quantization import per_group_quant, per_row_matmul, per_row_quant
+    x = torch.randn(4, 256, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(AssertionError):
+        per_row_quant(x, torch.float16)                       # dtype not in [int8, e4m3]
+    with pytest.raises(AssertionError):
+        per_row_quant(x.view(2, 2, 256), torch.int8)          # x.dim() != 2
+    with pytest.raises(AssertionError):
+        per_group_quant(x, 96, torch.int8)                    # K % group_size != 0
+    w = torch.randn(8, 192, dtype=torch.bfloat16, device="cuda")
+    qw, sw = per_row_quant(w, torch.int8)
+    with pytest.raises(AssertionError):
+        per_row_matmul(torch.randn(4, 192, dtype=torch.bfloat16, device="cuda"), qw, sw, None,
+                       torch.int8)                            # K % 128 != 0
+
+
+# ------------------------------------------------------------------ full-size properties
+
+@pytest.mark.parametrize("M,N,K", [(4096, 4096, 1024), (8192, 1024, 3072), (2048, 6144, 4096)])
+def test_full_size_int8_checksums(ext, M, N, K):
+    """BASELINE-size shapes: row and column checksums of the int32 accumulators, computed
+    independently in int64 on the device (sum_n acc[m,n] == qx[m,:] . sum_n qw[n,:])."""
+    qx, qw = rand_i8((M, K), 1).cuda(), rand_i8((N, K), 2).cuda()
+    acc = ext.gemm_i8_acc(qx, qw).to(torch.int64)
+    col_w = qw.to(torch.int64).sum(0)
+    row_x = qx.to(torch.int64).sum(0)
+    assert torch.equal(acc.sum(1), (qx.to(torch.int64) * col_w).sum(1))
+    assert torch.equal(acc.sum(0), (qw.to(torch.int64) * row_x).sum(1))
+    # spot-check 64 random entries exactly
+    g = torch.Generator().manual_seed(3)
+    mi = torch.randint(0, M, (64,), generator=g).cuda()
+    ni = torch.randint(0, N, (64,), generator=g).cuda()
+    exact = (qx[mi].to(torch.int64) * qw[ni].to(torch.int64)).sum(1)
+    assert torch.equal(acc[mi, ni], exact)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+def test_full_size_linearity_and_path_agreement(ext, dn):
+    """Scaling an activation row by 2 (exact in bf16) must scale that output row by exactly 2
+    (per-token scales absorb it), and the GEMV and GEMM paths must agree on shared rows."""
+    M, N, K = 4096, 4096, 1024
+    x = rand_bf16((M, K), 21).cuda()
+    w = rand_bf16((N, K), 22, 0.02).cuda()
+    qw, sw = ext.quant_rows(w, DT[dn])
+    y1 = ext.linear(x, qw, sw, None, DT[dn])
+    y2 = ext.linear(x * 2, qw, sw, None, DT[dn])
+    assert torch.equal(y2.float(), y1.float() * 2)
+    yv = ext.linear(x[:16].contiguous(), qw, sw, None, DT[dn])      # M <= 16 -> GEMV path
+    if dn == "i8":
+        assert torch.equal(yv, y1[:16])
+    else:
+        assert_close_fp(bits(yv), bits(y1[:16].contiguous()))
+
+
+# ------------------------------------------------------------------ layers, graphs
+
+def test_linear_dispatch_and_cuda_graph(ext):
+    from nanovllm.layers.linear import MergedColumnParallelLinear, RowParallelLinear
+    torch.manual_seed(0)
+    with torch.device("cuda"):
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(torch.bfloat16)
+        try:
+            up = MergedColumnParallelLinear(1024, [3072, 3072])
+            down = RowParallelLinear(3072, 1024)
+        finally:
+            torch.set_default_dtype(prev)
+    up.weight.data.normal_(0, 0.02)
+    down.weight.data.normal_(0, 0.02)
+    w_up = up.weight.data.clone()
+    up.quantize_(torch.int8)
+    down.quantize_(torch.float8_e4m3fn, "per_group", 128)
+    assert up.weight is None and up.qw.dtype == torch.int8 and up.sw.shape == (6144,)
+    assert down.sw.shape == (1024, 24)
+    for M in (4, 48):
+        x = torch.randn(M, 1024, dtype=torch.bfloat16, device="cuda")
+        h = up(x)
+        qx, sx = orc.quant_rows(bits(x), orc.INT8)
+        yo = orc.gemm_rows(qx, sx, bits(up.qw), bits(up.sw), None, orc.INT8)
+        assert np.array_equal(bits(h), yo)
+        assert _rel_err(h, x @ w_up.T) < 0.08
+        y = down(h[:, :3072].contiguous())
+        assert y.shape == (M, 1024)
+    # CUDA-graph capture (the reference captures decode, model_runner.py:316-356)
+    xs = torch.randn(8, 1024, dtype=torch.bfloat16, device="cuda")
+    eager = up(xs).clone()
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        up(xs)
+        with torch.cuda.graph(g, stream=s):
+            out = up(xs)
+    torch.cuda.current_stream().wait_stream(s)
+    xs.copy_(xs * 0.5)
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, up(xs))
+    assert torch.equal(out.float() * 2, eager.float())
