@@ -1,0 +1,384 @@
+#!/usr/bin/env python
+"""bench.py -- the quantized-linear hot path of Qwen3 through the B200-native engine.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--model 0.6b|1.7b|8b] [--tokens T] [--dtype int8|fp8] [--quant per_row|per_group]
+
+A "step" is one pass of the hot path over one batch of synthetic tokens: all 4 x n_layers
+quantized linears of the model (qkv -> o -> gate_up -> down per layer, distinct random-init
+weights per layer, so one pass streams every weight once and the working set exceeds L2).
+Default workload = BASELINE.json configs[1]/[0] shapes: Qwen3-0.6B, W8A8 INT8 per-row,
+T = 4096 tokens (8 x 512) per rank.
+
+N > 1 (launched by torchrun, one rank per GPU): the model is tensor-parallel TP = N exactly
+as nano-vllm shards it (column-parallel qkv/gate_up, row-parallel o/down + NCCL all-reduce);
+the batch grows with N (T x N tokens, "weak"), every rank sees every token.
+
+One JSON line on rank 0 (contract in the task statement): value = tokens/s with inputs
+resident in HBM; e2e = same metric with HOST (pinned) input/output buffers and the copies
+inside the timed region; roofline = the dominant kernel (tcgen05 GEMM) timed alone with CUDA
+events over the same weights; cpu_baseline = the reference's CPU path (torch dequant+matmul,
+oracle.ref_per_group_matmul) on a bounded sample.  --impl reference prints the CPU arm only.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "nano-vllm-hw3_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+MODELS = {  # hidden, intermediate, layers, heads, kv_heads, head_dim   
+    "0.6b": dict(hidden=1024, inter=3072, layers=28, heads=16, kv=8, hd=128),
+    "1.7b": dict(hidden=2048, inter=6144, layers=28, heads=16, kv=8, hd=128),
+    "8b": dict(hidden=4096, inter=12288, layers=36, heads=32, kv=8, hd=128),
+}
+METRIC = "qwen3_w8a8_linear_stack_tokens_per_s"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], bf16=d["bf16_tflops"], bf16_sus=d["bf16_tflops_sustained"],
+                    src="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src="fallback (B200_PROFILING.md)")
+
+
+def layer_shapes(m, tp=1):
+    """[(name, N, K)] per rank for one decoder layer."""
+    qkv_n = (m["heads"] + 2 * m["kv"]) * m["hd"]
+    return [("qkv", qkv_n // tp, m["hidden"]), ("o", m["hidden"], m["heads"] * m["hd"] // tp),
+            ("gate_up", 2 * m["inter"] // tp, m["hidden"]), ("down", m["hidden"], m["inter"] // tp)]
+
+
+def flops_bytes(M, shapes, group=0):
+    """Algorithmic work of one layer: FLOPs = 2MNK; bytes = quant
+    (2MK + MK + 4M) + GEMM (MK + NK + 4M + S_w + 2MN) for M > 16, fused (2MK + NK + S_w + 2MN) else."""
+    fl = by = 0
+    for _, N, K in shapes:
+        fl += 2 * M * N * K
+        sw = 4 * N * (K // group if group else 1)
+        by += (2 * M * K + N * K + sw + 2 * M * N) if M <= 16 else \
+              (3 * M * K + 4 * M) + (M * K + N * K + 4 * M + sw + 2 * M * N)
+    return fl, by
+
+
+# ------------------------------------------------------------------ clocks sampler
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, dev_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100", "-i", str(dev_index)], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            c = [t.strip() for t in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); pw.append(float(c[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.f.name)
+        if sm:
+            s = sorted(sm)
+            out.update(sm_mhz=s[len(s) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons),
+                       samples=len(sm), power_w_max=max(pw))
+        return out
+
+
+# ------------------------------------------------------------------ the stack under test
+
+class LinearStack:
+    """n_layers x (qkv, o, gate_up, down) built from the engine's own TP layer classes."""
+
+    def __init__(self, m, dtype, quant, group, device, seed=0):
+        from nanovllm.layers.linear import (MergedColumnParallelLinear, QKVParallelLinear,
+                                            RowParallelLinear)
+        self.m = m
+        prev = torch.get_default_dtype()
+        torch.set_default_dtype(torch.bfloat16)
+        g = torch.Generator(device=device).manual_seed(seed)
+        self.layers = []
+        with torch.device(device):
+            for _ in range(m["layers"]):
+                mods = [QKVParallelLinear(m["hidden"], m["hd"], m["heads"], m["kv"]),
+                        RowParallelLinear(m["heads"] * m["hd"], m["hidden"]),
+                        MergedColumnParallelLinear(m["hidden"], [m["inter"]] * 2),
+                        RowParallelLinear(m["inter"], m["hidden"])]
+                for mod in mods:
+                    mod.weight.data.normal_(0.0, 0.02, generator=g)   # random-init (no checkpoints offline)
+                    mod.quantize_(dtype, quant, group)
+                self.layers.append(mods)
+        torch.set_default_dtype(prev)
+        self.tp = self.layers[0][0].tp_size
+
+    @torch.inference_mode()
+    def forward(self, x):
+        """x bf16 [T, hidden] -> bf16 [T, hidden].  Attention / SiLU / norms are outside the
+        hot path: the o_proj and down_proj inputs are the leading columns of the previous
+        output (a strided view, exercising ldx), and every layer starts from x again."""
+        m = self.m
+        k_o, k_down = m["heads"] * m["hd"] // self.tp, m["inter"] // self.tp
+        y = x
+        for qkv, o, gate_up, down in self.layers:
+            h = qkv(x)
+            h = o(h[:, :k_o])
+            h = gate_up(h)
+            y = down(h[:, :k_down])
+        return y
+
+
+def time_steps(fn, steps, warmup, dist_on):
+    import torch.distributed as dist
+    for _ in range(warmup):
+        fn()
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    for _ in range(steps):
+        fn()
+    ev[1].record()
+    torch.cuda.synchronize()
+    ms = ev[0].elapsed_time(ev[1])
+    if dist_on:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        ms = float(t.item())
+    return ms / steps
+
+
+# ------------------------------------------------------------------ CPU arm
+
+def cpu_reference(m, T, dtype, quant, group, n_layers_sample, reps):
+    """The reference's CPU quantized-linear path (per_group_quant + per_group_matmul with
+    group_size = K for the per-row layout; quantization.py:194-234, 265-307) as restated in
+    oracle.ref_per_group_*; fp32 SGEMM on all host threads."""
+    from oracle import oracle as orc
+    torch.set_num_threads(os.cpu_count() or 1)
+    g = torch.Generator().manual_seed(0)
+    shapes = layer_shapes(m)
+    layers = []
+    for _ in range(n_layers_sample):
+        ws = []
+        for _, N, K in shapes:
+            w = (torch.randn(N, K, generator=g) * 0.02).to(torch.bfloat16)
+            gs = group if quant == "per_group" else K
+            ws.append((orc.ref_per_group_quant(w, gs, dtype), gs))
+        layers.append(ws)
+    x = torch.randn(T, m["hidden"], generator=torch.Generator().manual_seed(1)).to(torch.bfloat16)
+    k_o, k_down = m["heads"] * m["hd"], m["inter"]
+
+    def one_pass():
+        for (qkv, o, gu, dn) in layers:
+            h = orc.ref_per_group_matmul(x, qkv[0][0], qkv[0][1], None, qkv[1], dtype)
+            h = orc.ref_per_group_matmul(h[:, :k_o].contiguous(), o[0][0], o[0][1], None, o[1], dtype)
+            h = orc.ref_per_group_matmul(h, gu[0][0], gu[0][1], None, gu[1], dtype)
+            orc.ref_per_group_matmul(h[:, :k_down].contiguous(), dn[0][0], dn[0][1], None, dn[1], dtype)
+
+    one_pass()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        one_pass()
+        ts.append(time.perf_counter() - t0)
+    ts.sort()
+    t_layer = ts[len(ts) // 2] / n_layers_sample
+    tok_s = T / (t_layer * m["layers"])
+    return tok_s, t_layer, torch.get_num_threads()
+
+
+# ------------------------------------------------------------------ main
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="0.6b", choices=list(MODELS))
+    ap.add_argument("--tokens", type=int, default=4096, help="tokens per rank per step")
+    ap.add_argument("--dtype", default="int8", choices=["int8", "fp8"])
+    ap.add_argument("--quant", default="per_row", choices=["per_row", "per_group"])
+    ap.add_argument("--group-size", type=int, default=128)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    m = MODELS[args.model]
+    dtype = torch.int8 if args.dtype == "int8" else torch.float8_e4m3fn
+    group = args.group_size if args.quant == "per_group" else 0
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    T_rank = args.tokens
+    workload = (f"qwen3-{args.model} linear stack ({4 * m['layers']} quantized linears: qkv,o,gate_up,down x "
+                f"{m['layers']} layers), {args.dtype} {args.quant}"
+                + (f" g={group}" if group else "") + f", {T_rank} tokens/rank/step")
+
+    # ---------------------------------------------------------------- reference (CPU) arm
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        T_s = min(T_rank, 4096)
+        for _ in range(max(args.warmup - 1, 0)):
+            pass                                            # warm-up pass is inside cpu_reference
+        tok_s, t_layer, cores = cpu_reference(m, T_s, dtype, args.quant, group, 2, max(args.steps, 1))
+        line = {
+            "impl": "reference", "metric": METRIC, "value": tok_s, "unit": "tokens/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_layer * m["layers"] * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic (random-init weights, randn activations)",
+            "config": {"workload": workload, "arm": "reference CPU path: torch dequant + fp32 matmul"},
+            "cpu_baseline": {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port",
+                             "sample": f"2 of {m['layers']} layers x {T_s} tokens per step, median of "
+                                       f"{max(args.steps, 1)} steps after 1 warm-up, scaled to {m['layers']} layers"},
+            "e2e": {"value": tok_s, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+        }
+        print(json.dumps(line))
+        return
+
+    # ---------------------------------------------------------------- B200 arm
+    import torch.distributed as dist
+    assert torch.cuda.is_available(), "bench.py --impl b200 needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dist_on = world > 1
+    if dist_on:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from nanovllm import _ext
+    assert _ext.load().ql_device_check() == 0
+    peaks = load_peaks()
+
+    stack = LinearStack(m, dtype, args.quant, group, "cuda", seed=0)
+    T = T_rank * world                                     # every TP rank sees every token
+    gx = torch.Generator(device="cuda").manual_seed(1)
+    x_dev = torch.randn(T, m["hidden"], generator=gx, device="cuda", dtype=torch.float32).to(torch.bfloat16)
+    x_host = x_dev.cpu().pin_memory()
+    y_host = torch.empty((T, m["hidden"]), dtype=torch.bfloat16).pin_memory()
+    x_in = torch.empty_like(x_dev)
+
+    def step_dev():
+        return stack.forward(x_dev)
+
+    def step_e2e():
+        x_in.copy_(x_host, non_blocking=True)
+        y = stack.forward(x_in)
+        y_host.copy_(y, non_blocking=True)
+        torch.cuda.current_stream().synchronize()         # the caller reads the result on the host
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    n0 = _ext.launch_count()
+    ms = time_steps(step_dev, args.steps, args.warmup, dist_on)
+    launches_per_step = (_ext.launch_count() - n0) // (args.steps + args.warmup)
+    clocks = sampler.stop() if sampler else {}
+    ms_e2e = time_steps(step_e2e, args.steps, max(args.warmup, 3), dist_on)
+
+    # ---- dominant kernel alone (roofline): the GEMM (or GEMV for T <= 16) over all local weights
+    shapes = layer_shapes(m, world)
+    fl_layer, by_layer = flops_bytes(T, shapes, group)
+    n_lin = 4 * m["layers"]
+    acts = {}
+    for (_, N, K) in shapes:
+        if K not in acts:
+            xa = torch.randn(T, K, device="cuda", dtype=torch.float32, generator=gx).to(torch.bfloat16)
+            acts[K] = (xa,) + tuple(_ext.quant_rows(xa, dtype)) if T > 16 else (xa,)
+
+    def kernels_only():
+        for mods in stack.layers:
+            for mod in mods:
+                K = mod.qw.shape[1]
+                if T > 16:
+                    _ext.gemm_w8a8(acts[K][1], acts[K][2], mod.qw, mod._sw_kernel, None, dtype, mod.group_size)
+                else:
+                    _ext.gemv_w8a8(acts[K][0], mod.qw, mod._sw_kernel, None, dtype, mod.group_size)
+
+    ms_k = time_steps(kernels_only, max(args.steps // 2, 2), 3, False)
+    if T > 16:
+        k_fl = sum(2 * T * N * K for _, N, K in shapes) * m["layers"]
+        k_by = sum(T * K + N * K + 4 * T + 4 * N * (K // group if group else 1) + 2 * T * N
+                   for _, N, K in shapes) * m["layers"]
+    else:
+        k_fl, k_by = fl_layer * m["layers"], by_layer * m["layers"]
+    t_k = ms_k * 1e-3
+    tensor_peak = 2.0 * peaks["bf16"]                     # 8-bit dense rate = 2 x bf16 on sm_100
+    t_fl, t_by = k_fl / (tensor_peak * 1e12), k_by / (peaks["hbm"] * 1e9)
+    if t_fl >= t_by:
+        roof = {"bound": "tensor", "achieved": k_fl / t_k / 1e12, "peak": tensor_peak, "unit": "TFLOP/s"}
+    else:
+        roof = {"bound": "hbm", "achieved": k_by / t_k / 1e9, "peak": peaks["hbm"], "unit": "GB/s"}
+    roof["frac"] = roof["achieved"] / roof["peak"]
+    roof.update(traffic=None, kernel="gemm_kernel (tcgen05)" if T > 16 else "gemv_kernel",
+                launches=n_lin, avg_launch_us=ms_k * 1e3 / n_lin,
+                tflops=k_fl / t_k / 1e12, gbs=k_by / t_k / 1e9,
+                share_of_step=ms_k / ms,
+                peak_source=peaks["src"] + ("; tensor peak = 2 x measured bf16 burst (8-bit dense is 2x bf16)"
+                                            if roof["bound"] == "tensor" else ""))
+
+    line = {
+        "metric": METRIC, "value": T / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int8" if dtype == torch.int8 else "fp8_e4m3",
+        "data": "synthetic (random-init N(0,0.02) bf16 weights quantised on device, randn activations)",
+        "config": {"workload": workload, "tokens_per_step": T, "parallelism": f"tp{world}",
+                   "l2": "one step streams every layer's distinct weights + activations (> 126 MB L2 "
+                         "working set for the default); no explicit flush",
+                   "quant": args.quant, "group_size": group},
+        "tflops": fl_layer * m["layers"] / (ms * 1e-3) / 1e12,
+        "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": y_host.numel() * 2},
+        "gpu_launches": int(launches_per_step) * args.steps,
+        "gpu_launches_per_step": int(launches_per_step),
+        "roofline": roof, "clocks": clocks,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        T_s = min(T_rank, 4096)
+        tok_s, t_layer, cores = cpu_reference(m, T_s, dtype, args.quant, group, 2, 3)
+        line["cpu_baseline"] = {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port",
+                                "sample": f"2 of {m['layers']} layers x {T_s} tokens, median of 3 passes after "
+                                          f"1 warm-up, scaled to {m['layers']} layers"}
+    if rank == 0:
+        print(json.dumps(line))
+    if dist_on:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -69,6 +69,10 @@ QL_API const char* ql_status_string(int status);
 /* QL_OK when the current CUDA device can run the kernels (compute capability 10.x). */
 QL_API int ql_device_check(void);
 
+/* Number of CUDA kernels this library has launched in this process (monotonic; for bench.py's
+ * gpu_launches and for tests that assert the CUDA path -- not a fallback -- ran). */
+QL_API uint64_t ql_launch_count(void);
+
 /*
  * Per-row (per-token) symmetric quantiser.
  * Replaces per_row_quant / _per_row_quant_kernel, nanovllm/utils/quantization.py:13-51,147-163:

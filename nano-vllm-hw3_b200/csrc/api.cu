@@ -32,6 +32,9 @@ int num_sms() {
   return d.sms > 0 ? d.sms : 148;
 }
 
+static unsigned long long g_launches = 0;
+void count_launch(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
+
 static int check_arch() {
   const DevInfo d = query_device();
   if (d.ok < 0) return QL_ERR_CUDA;
@@ -66,6 +69,8 @@ const char* ql_status_string(int status) {
 }
 
 int ql_device_check(void) { return check_arch(); }
+
+uint64_t ql_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
 int ql_quant_rows(const void* x, int64_t M, int64_t K, int64_t ldx, int fmt, void* q, float* s,
                   ql_stream_t stream) {

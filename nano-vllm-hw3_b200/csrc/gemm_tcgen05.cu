@@ -318,6 +318,7 @@ static int launch_cfg(const void* qx, const void* qw, GemmParams p, cudaStream_t
   const int64_t tiles = (int64_t)p.tiles_n * p.tiles_m;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   kern<<<grid, kGemmThreads, Cfg::smem_bytes, st>>>(tm_w, tm_x, p);
+  count_launch();
   return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
 }
 

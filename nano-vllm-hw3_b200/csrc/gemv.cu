@@ -247,6 +247,7 @@ static int launch_one(const GemvParams& p, cudaStream_t st) {
   int64_t grid = (int64_t)num_sms() * occ;
   if (grid > iters) grid = iters;
   kern<<<(unsigned)grid, kGemvThreads, smem, st>>>(p);
+  count_launch();
   return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
 }
 

@@ -27,4 +27,7 @@ int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw
 
 int num_sms();
 
+// Every kernel launch of the library bumps this (read through ql_launch_count()).
+void count_launch(int n = 1);
+
 }  // namespace ql

@@ -143,6 +143,7 @@ int launch_quant_tensor(const void* x, int64_t numel, int fmt, void* q, void* sc
     tensor_quant_kernel<QL_FP8_E4M3><<<(unsigned)blocks, 256, 0, st>>>(
         xp, numel, static_cast<const uint32_t*>(ws), static_cast<uint8_t*>(q),
         static_cast<uint16_t*>(scale_bf16));
+  count_launch(2);
   return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
 }
 
@@ -162,6 +163,7 @@ static int launch_quant_rows_fmt(const void* x, int64_t M, int64_t K, int64_t ld
     quant_rows_kernel<FMT, 16><<<blocks, 256, 0, st>>>(xp, M, (int)K, ldx, qp, s);
   else
     quant_rows_kernel<FMT, 0><<<blocks, 256, 0, st>>>(xp, M, (int)K, ldx, qp, s);
+  count_launch();
   return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
 }
 
@@ -183,6 +185,7 @@ int launch_quant_groups(const void* w, int64_t N, int64_t K, int64_t g, int fmt,
     quant_groups_kernel<QL_INT8><<<blocks, 256, 0, st>>>(wp, N, (int)K, (int)g, qp, s);
   else
     quant_groups_kernel<QL_FP8_E4M3><<<blocks, 256, 0, st>>>(wp, N, (int)K, (int)g, qp, s);
+  count_launch();
   return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
 }
 

@@ -29,6 +29,7 @@ SIGNATURES = {
     "ql_version": (_c_int, []),
     "ql_status_string": (ctypes.c_char_p, [_c_int]),
     "ql_device_check": (_c_int, []),
+    "ql_launch_count": (ctypes.c_uint64, []),
     "ql_quant_rows": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "ql_quant_groups": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "ql_quant_tensor": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
@@ -220,6 +221,11 @@ def gemv_w8a8(x, qw, sw, bias, dtype, group_size: int = 0):
         _check(load().ql_gemv_w8a8(_ptr(x2), x2.stride(0) if M > 1 else K, _ptr(qw), _ptr(sw),
                                    _ptr(bias), _ptr(y), N, M, N, K, fmt, group_size, _stream(x)))
     return y.view(y_shape)
+
+
+def launch_count() -> int:
+    """Kernels launched by the library so far in this process."""
+    return int(load().ql_launch_count())
 
 
 def linear_path(M: int, N: int, K: int, group_size: int = 0) -> str:
