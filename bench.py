@@ -240,6 +240,7 @@ def main():
     ap.add_argument("--quant", default="per_row", choices=["per_row", "per_group"])
     ap.add_argument("--group-size", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="never replay a CUDA graph (T <= 512 does by default)")
     args = ap.parse_args()
 
     m = MODELS[args.model]
@@ -295,19 +296,48 @@ def main():
     y_host = torch.empty((T, m["hidden"]), dtype=torch.bfloat16).pin_memory()
     x_in = torch.empty_like(x_dev)
 
+    # Decode-sized batches replay a CUDA graph of the whole pass, exactly as the reference engine
+    # does for decode (ModelRunner.capture_cudagraph, model_runner.py:316-356: bs <= 512);
+    # prefill-sized batches run eagerly (model_runner.py:283-284).
+    use_graph = T <= 512 and not args.no_graph
+    graph_out = {}
+
+    def capture(x_buf):
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            stack.forward(x_buf)                           # warm-up outside capture
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=s):
+                out = stack.forward(x_buf)
+        torch.cuda.current_stream().wait_stream(s)
+        return gr, out
+
+    if use_graph:
+        graph_out["dev"] = capture(x_dev)
+        graph_out["e2e"] = capture(x_in)
+
     def step_dev():
+        if use_graph:
+            graph_out["dev"][0].replay()
+            return graph_out["dev"][1]
         return stack.forward(x_dev)
 
     def step_e2e():
         x_in.copy_(x_host, non_blocking=True)
-        y = stack.forward(x_in)
+        if use_graph:
+            graph_out["e2e"][0].replay()
+            y = graph_out["e2e"][1]
+        else:
+            y = stack.forward(x_in)
         y_host.copy_(y, non_blocking=True)
         torch.cuda.current_stream().synchronize()         # the caller reads the result on the host
 
     sampler = ClockSampler(local) if rank == 0 else None
     n0 = _ext.launch_count()
+    stack.forward(x_dev)                                   # one eager pass counts the launches/step
+    launches_per_step = _ext.launch_count() - n0
     ms = time_steps(step_dev, args.steps, args.warmup, dist_on)
-    launches_per_step = (_ext.launch_count() - n0) // (args.steps + args.warmup)
     clocks = sampler.stop() if sampler else {}
     ms_e2e = time_steps(step_e2e, args.steps, max(args.warmup, 3), dist_on)
 
@@ -330,7 +360,18 @@ def main():
                 else:
                     _ext.gemv_w8a8(acts[K][0], mod.qw, mod._sw_kernel, None, dtype, mod.group_size)
 
-    ms_k = time_steps(kernels_only, max(args.steps // 2, 2), 3, False)
+    if use_graph:
+        ks = torch.cuda.Stream()
+        ks.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(ks):
+            kernels_only()
+            kgr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(kgr, stream=ks):
+                kernels_only()
+        torch.cuda.current_stream().wait_stream(ks)
+        ms_k = time_steps(kgr.replay, max(args.steps // 2, 2), 3, False)
+    else:
+        ms_k = time_steps(kernels_only, max(args.steps // 2, 2), 3, False)
     if T > 16:
         k_fl = sum(2 * T * N * K for _, N, K in shapes) * m["layers"]
         k_by = sum(T * K + N * K + 4 * T + 4 * N * (K // group if group else 1) + 2 * T * N
@@ -360,7 +401,8 @@ def main():
         "config": {"workload": workload, "tokens_per_step": T, "parallelism": f"tp{world}",
                    "l2": "one step streams every layer's distinct weights + activations (> 126 MB L2 "
                          "working set for the default); no explicit flush",
-                   "quant": args.quant, "group_size": group},
+                   "quant": args.quant, "group_size": group,
+                   "launch": "cuda graph replay" if use_graph else "eager"},
         "tflops": fl_layer * m["layers"] / (ms * 1e-3) / 1e12,
         "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": y_host.numel() * 2},

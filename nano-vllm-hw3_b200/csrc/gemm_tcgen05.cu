@@ -48,19 +48,24 @@ constexpr int kGemmThreads = 256;
 constexpr int kTileN = 128;   // weight rows per tile (UMMA M)
 constexpr int kBlockK = 128;  // bytes of K per pipeline stage (one 128B swizzle atom)
 constexpr int kSmemBudget = 227 * 1024;
+// epilogue staging per epilogue warp: a [32 tokens][32 features] bf16 tile (64-byte rows) used to
+// transpose the accumulator (feature on the TMEM lane) into token-major 16-byte global stores,
+// plus the 32 per-token scales of the chunk
+constexpr int kEpiWarpSmem = 32 * 32 * 2 + 32 * 4;
+constexpr int kEpiSmem = 4 * kEpiWarpSmem;
 
 template <int BT> struct GemmCfg {
   static constexpr int stage_a = kTileN * kBlockK;
   static constexpr int stage_b = BT * kBlockK;
   static constexpr int stage = stage_a + stage_b;
-  static constexpr int stages_raw = (kSmemBudget - 2048) / stage;
+  static constexpr int stages_raw = (kSmemBudget - 2048 - kEpiSmem) / stage;
   static constexpr int stages = stages_raw > 8 ? 8 : stages_raw;
   static constexpr int nacc_raw = 512 / BT;
   static constexpr int nacc = nacc_raw > 4 ? 4 : nacc_raw;
   static constexpr int tmem_cols_raw = nacc * BT;
   static constexpr int tmem_cols = tmem_cols_raw <= 32 ? 32 : tmem_cols_raw <= 64 ? 64
                                    : tmem_cols_raw <= 128 ? 128 : tmem_cols_raw <= 256 ? 256 : 512;
-  static constexpr int smem_bytes = stages * stage + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int smem_bytes = stages * stage + 1024 /*align slack*/ + 256 /*barriers*/ + kEpiSmem;
 };
 
 template <int FMT, bool GROUPED, int BT, bool OUT_ACC>
@@ -81,6 +86,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + NACC;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + NACC);
+  uint8_t* epi_smem = smem + STAGES * Cfg::stage + 256;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -174,42 +180,101 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue (TMEM -> registers -> global) =====================
+    // ===================== epilogue (TMEM -> registers -> smem transpose -> global) ==========
     const int q = warp - 4;  // TMEM lane quarter: this warp reads lanes [32q, 32q+32)
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    uint16_t* stg = reinterpret_cast<uint16_t*>(epi_smem + q * kEpiWarpSmem);  // [32 m][32 n]
+    float* sxs = reinterpret_cast<float*>(stg + 32 * 32);                      // [32 m]
+    const bool vec_ok = (p.ldy % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15) == 0);
     int acc = 0;
     uint32_t acc_phase = 0;
+
+    // v[i] = value of (token mc + i, this thread's feature n), already scaled; -> bf16 -> y
+    auto store_chunk = [&](const float (&v)[32], int mc, int nq0) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) stg[i * 32 + lane] = f2bf(v[i]);
+      __syncwarp();
+      if (vec_ok) {
+        const int nb = nq0 + (lane & 3) * 8;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int row = j * 8 + (lane >> 2);
+          const int m = mc + row;
+          const uint4 val = *reinterpret_cast<const uint4*>(stg + row * 32 + (lane & 3) * 8);
+          if (m < p.M) {
+            uint16_t* dst = p.y + (int64_t)m * p.ldy + nb;
+            if (nb + 8 <= p.N) {
+              *reinterpret_cast<uint4*>(dst) = val;
+            } else if (nb < p.N) {
+              const uint16_t* sv = stg + row * 32 + (lane & 3) * 8;
+              for (int e = 0; e < p.N - nb; ++e) dst[e] = sv[e];
+            }
+          }
+        }
+      } else {
+        const int n = nq0 + lane;
+        for (int row = 0; row < 32; ++row) {
+          const int m = mc + row;
+          if (m < p.M && n < p.N) p.y[(int64_t)m * p.ldy + n] = stg[row * 32 + lane];
+        }
+      }
+      __syncwarp();
+    };
+
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int tn = tile % p.tiles_n, tm = tile / p.tiles_n;
-      const int n = tn * kTileN + q * 32 + lane;
+      const int nq0 = tn * kTileN + q * 32;
+      const int n = nq0 + lane;
       const bool n_ok = n < p.N;
       const int m0 = tm * BT;
-      const float biasv = (p.bias != nullptr && n_ok) ? bf16_lo(p.bias[n]) : 0.0f;
+      const bool has_bias = p.bias != nullptr;
+      const float biasv = (has_bias && n_ok) ? bf16_lo(p.bias[n]) : 0.0f;
 
-      if constexpr (!GROUPED) {
-        const float swn = (!OUT_ACC && n_ok) ? __ldg(p.sw + n) : 0.0f;
+      if constexpr (OUT_ACC) {
         mbar_wait(&tfull_bar[acc], acc_phase);
         tc_fence_after();
 #pragma unroll 1
         for (int c = 0; c < BT / 32; ++c) {
           uint32_t r[32];
           tmem_ld32(lane_addr + acc * BT + c * 32, r);
-          const int mc = m0 + c * 32;
-          const float sx_l = (!OUT_ACC && mc + lane < p.M) ? __ldg(p.sx + mc + lane) : 0.0f;
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
-            const int m = mc + i;
-            if constexpr (OUT_ACC) {
-              if (m < p.M && n_ok) p.acc_out[(int64_t)m * p.N + n] = (int32_t)r[i];
-            } else {
-              const float sxm = __shfl_sync(0xffffffffu, sx_l, i);
-              const float a = FMT == QL_INT8 ? __int2float_rn((int)r[i]) : __uint_as_float(r[i]);
-              float v = __fmul_rn(__fmul_rn(a, sxm), swn);  // (acc * sa) * sb
-              if (p.bias != nullptr) v = __fadd_rn(v, biasv);
-              if (m < p.M && n_ok) p.y[(int64_t)m * p.ldy + n] = f2bf(v);
+            const int m = m0 + c * 32 + i;
+            if (m < p.M && n_ok) p.acc_out[(int64_t)m * p.N + n] = (int32_t)r[i];
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        if (++acc == NACC) { acc = 0; acc_phase ^= 1; }
+      } else if constexpr (!GROUPED) {
+        const float swn = n_ok ? __ldg(p.sw + n) : 0.0f;
+        mbar_wait(&tfull_bar[acc], acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BT / 32; ++c) {
+          const int mc = m0 + c * 32;
+          if (mc >= p.M) break;  // whole chunk past the last token (warp-uniform)
+          uint32_t r[32];
+          tmem_ld32(lane_addr + acc * BT + c * 32, r);
+          sxs[lane] = (mc + lane < p.M) ? __ldg(p.sx + mc + lane) : 0.0f;
+          __syncwarp();
+          tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            const float4 s4 = *reinterpret_cast<const float4*>(sxs + i);
+            const float sxv[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float a = FMT == QL_INT8 ? __int2float_rn((int)r[i + e]) : __uint_as_float(r[i + e]);
+              float t = __fmul_rn(__fmul_rn(a, sxv[e]), swn);  // (acc * sa) * sb, reference :121
+              if (has_bias) t = __fadd_rn(t, biasv);
+              v[i + e] = t;
             }
           }
+          store_chunk(v, mc, nq0);
         }
         tc_fence_before();
         __syncwarp();
@@ -246,14 +311,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
 #pragma unroll
         for (int c = 0; c < BT / 32; ++c) {
           const int mc = m0 + c * 32;
-          const float sx_l = (mc + lane < p.M) ? __ldg(p.sx + mc + lane) : 0.0f;
+          if (mc < p.M) {
+            sxs[lane] = (mc + lane < p.M) ? __ldg(p.sx + mc + lane) : 0.0f;
+            __syncwarp();
+            float v[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int m = mc + i;
-            const float sxm = __shfl_sync(0xffffffffu, sx_l, i);
-            float v = __fmul_rn(t[c * 32 + i], sxm);
-            if (p.bias != nullptr) v = __fadd_rn(v, biasv);
-            if (m < p.M && n_ok) p.y[(int64_t)m * p.ldy + n] = f2bf(v);
+            for (int i = 0; i < 32; ++i) {
+              float u = __fmul_rn(t[c * 32 + i], sxs[i]);
+              if (has_bias) u = __fadd_rn(u, biasv);
+              v[i] = u;
+            }
+            store_chunk(v, mc, nq0);
           }
         }
       }
