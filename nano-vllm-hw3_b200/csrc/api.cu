@@ -156,8 +156,8 @@ size_t ql_workspace_bytes(int64_t M, int64_t K) {
 }
 
 const char* ql_linear_path(int64_t M, int64_t N, int64_t K, int64_t group) {
-  (void)N; (void)K; (void)group;
-  return M <= 16 ? "gemv_mma" : "gemm_tcgen05";
+  if (M <= 16) return "gemv_mma";
+  return gemm_kernel_choice(M, N, K, group) == 2 ? "gemm_tcgen05_2cta" : "gemm_tcgen05";
 }
 
 int ql_linear(const void* x, int64_t ldx, const void* qw, const float* sw, const void* bias,

@@ -263,4 +263,18 @@ __host__ __device__ constexpr uint32_t make_idesc(uint32_t umma_m, uint32_t umma
   return d;
 }
 
+// ------------------------------------------------------------------ persistent tile order
+
+// Tile order: token tiles vary fastest inside super-groups of `group_m` token tiles, so the
+// tiles in flight at any moment share a few weight tiles and a set of activation tiles that
+// stays L2-resident, and every weight tile is fetched from HBM once per super-group.
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group_m,
+                                            int& tm, int& tn) {
+  const int per_group = group_m * tiles_n;
+  const int g = tile / per_group, r = tile - g * per_group;
+  const int gm = min(group_m, tiles_m - g * group_m);
+  tn = r / gm;
+  tm = g * group_m + (r - tn * gm);
+}
+
 }  // namespace ql

@@ -1,0 +1,468 @@
+// Prefill-regime W8A8 GEMM: CTA-pair (cta_group::2) tcgen05 kernel with per-row scales.
+// Replaces the reference's Triton kernel _per_row_post_process_mm
+// (nanovllm/utils/quantization.py:54-144) for token counts that fill the machine.
+//
+// Why a second GEMM kernel: at Qwen3 shapes K is short (1024..4096), so a tile's operands are
+// loaded once per output tile and the L2 -> shared-memory stream, not the tensor pipe, is the
+// first limit.  A CTA pair computes a 256-token x 256-feature tile with ONE
+// tcgen05.mma.cta_group::2 (UMMA 256x256x32): each CTA stages only its own 128 token rows (A)
+// and HALF of the 256 weight rows (B); the tensor core reads the other half from the peer's
+// shared memory.  Per CTA that is 32 KB of operands per 128-byte K block for 128x256 outputs
+// (256 FLOP per L2 byte, against 128 for the single-CTA 128x128 tile).
+//
+// Orientation: tokens on the TMEM lanes, features on the TMEM columns.  An epilogue thread owns
+// one token row; after tcgen05.ld it holds 32 consecutive features of that token, applies
+// (float(acc) * sx[m]) * sw[n] (+ bias[n]) -- the reference's product order, :111-121 -- packs
+// bf16 pairs and writes 16-byte pieces into a 128B-swizzled staging tile that one lane hands
+// to the TMA store engine (cp.async.bulk.tensor ... global.shared::cta).  No per-element
+// address arithmetic, no transposition, stores fully coalesced by the TMA unit.
+//
+// Pipeline per CTA (256 threads; both CTAs of a pair run the same roles except the MMA issue):
+//   warp 0 / lane 0  TMA producer: own A rows + own half of B per K block -> STAGES-deep ring;
+//                    completion bytes are counted on the LEADER CTA's `full` barrier
+//   warp 1 / lane 0  (leader CTA only) MMA issuer; tcgen05.commit multicast to both CTAs frees
+//                    the ring slot (`empty`) and publishes the accumulator (`tfull`)
+//   warp 2           TMEM allocator (512 columns = two 256-column accumulators)
+//   warps 4-7        epilogue (TMEM -> registers -> scales -> bf16 -> smem -> TMA store);
+//                    arrives on the leader's `tempty` when an accumulator has been drained
+#include <cuda.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ql {
+
+struct Gemm2Params {
+  const float* sx;       // [M]
+  const float* sw;       // [N]
+  const uint16_t* bias;  // bf16 [N] or nullptr
+  int32_t* acc_out;      // int32 [M, N] (OUT_ACC only)
+  int M, N, K;
+  int tiles_m, tiles_n;  // pair tiles (256 tokens x 256 features)
+  int group_m;           // token tiles per rasterisation super-group
+};
+
+constexpr int kG2Threads = 256;
+constexpr int kG2RowsA = 128;    // token rows per CTA (UMMA M = 256 per pair)
+constexpr int kG2TileN = 256;    // features per pair tile (UMMA N)
+constexpr int kG2RowsB = 128;    // weight rows staged per CTA (half of the tile)
+constexpr int kG2BlockK = 128;   // bytes of K per stage (one 128B swizzle atom)
+constexpr int kG2Stages = 5;
+constexpr int kG2StageA = kG2RowsA * kG2BlockK;
+constexpr int kG2StageB = kG2RowsB * kG2BlockK;
+constexpr int kG2Stage = kG2StageA + kG2StageB;                 // 32 KB
+constexpr int kG2StoreCols = 64;                                // bf16 columns per TMA store box (128 B)
+constexpr int kG2StageOut = 32 * kG2StoreCols * 2;              // 4 KB: [32 tokens][64 features]
+constexpr int kG2EpiSmem = 4 * 2 * kG2StageOut;                 // 4 warps x 2 buffers
+constexpr int kG2VecSmem = 2 * 2 * kG2TileN * 4;                // sw / bias tiles, double buffered
+constexpr int kG2Smem = kG2Stages * kG2Stage + kG2EpiSmem + kG2VecSmem + 256 + 1024;
+
+// ---- cluster / peer helpers -----------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::
+                   : "memory");
+}
+// shared::cluster address of `local` (a shared::cta address) inside CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load issued by either CTA of a pair; completion bytes land on the barrier at cluster
+// address `bar_cluster` (the leader's)
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const void* desc,
+                                                 uint32_t bar_cluster, int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(desc), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const void* desc, uint32_t smem_src, int32_t c0,
+                                             int32_t c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   desc),
+               "r"(smem_src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() {
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* smem_out, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(smem_out)),
+               "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish2() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t addr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(ncols)
+               : "memory");
+}
+// commit all prior MMAs of this thread; arrive on the barrier at the same offset in both CTAs
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
+      "[%0], %1;" ::"r"(smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void mma2_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                        uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma2_f8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                        uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c,
+                                       uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c),
+               "r"(d)
+               : "memory");
+}
+__device__ __forceinline__ float4 lds128f(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts32f(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
+template <int FMT, bool OUT_ACC>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kG2Threads, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+             const __grid_constant__ CUtensorMap tm_y, const Gemm2Params p) {
+  static_assert(!(OUT_ACC && FMT != QL_INT8), "raw accumulators: int8 only");
+  extern __shared__ uint8_t smem_raw[];
+  // all offsets below are identical in both CTAs of the pair (the MMA and the multicast
+  // commits address the peer's shared memory by offset)
+  const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t epi0 = smem0 + kG2Stages * kG2Stage;   // TMA-store staging, 1024-aligned
+  const uint32_t vec0 = epi0 + kG2EpiSmem;              // sw / bias tiles
+  uint8_t* smem_gen = smem_raw + (smem0 - smem_u32(smem_raw));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_gen + kG2Stages * kG2Stage + kG2EpiSmem +
+                                                   kG2VecSmem);
+  uint64_t* empty_bar = full_bar + kG2Stages;
+  uint64_t* tfull_bar = empty_bar + kG2Stages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();   // 0 = leader (issues the MMAs)
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_x);
+    tma_prefetch_desc(&tm_w);
+    tma_prefetch_desc(&tm_y);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kG2Stages; ++i) {
+      mbar_init(&full_bar[i], 1);    // the leader's arrive.expect_tx (bytes of BOTH CTAs)
+      mbar_init(&empty_bar[i], 1);   // one multicast tcgen05.commit
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull_bar[i], 1);   // one multicast tcgen05.commit
+      mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps x 2 CTAs
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    tmem_alloc2(tmem_slot, 512);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_kb = p.K / kG2BlockK;
+  const int total_tiles = p.tiles_m * p.tiles_n;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        int tm, tn;
+        tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+        const int row_a = tm * 2 * kG2RowsA + (int)cta * kG2RowsA;
+        const int row_b = tn * kG2TileN + (int)cta * kG2RowsB;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          // Both CTAs' bytes are counted on the leader's barrier; only the leader arrives
+          // (a local, fence-free operation).  The peer's bytes may land before the leader's
+          // expect_tx of the same phase: the transaction count goes negative transiently and
+          // the phase still cannot complete before the leader's arrival.
+          const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[stage]), 0);
+          if (cta == 0) mbar_expect_tx(&full_bar[stage], 2 * kG2Stage);
+          uint8_t* sa = smem_gen + stage * kG2Stage;
+          tma_load_2d_pair(sa, &tm_x, full_leader, kb * kG2BlockK, row_a);
+          tma_load_2d_pair(sa + kG2StageA, &tm_w, full_leader, kb * kG2BlockK, row_b);
+          if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (cta == 0 && lane == 0) {
+      constexpr uint32_t idesc = make_idesc<FMT>(2 * kG2RowsA, kG2TileN);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kG2TileN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem0 + stage * kG2Stage;
+          const uint64_t a_desc = make_sw128_kmajor_desc(sa);
+          const uint64_t b_desc = make_sw128_kmajor_desc(sa + kG2StageA);
+#pragma unroll
+          for (int k = 0; k < kG2BlockK / 32; ++k) {
+            const uint32_t accumulate = (kb > 0 || k > 0);
+            if constexpr (FMT == QL_INT8)
+              mma2_i8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, accumulate);
+            else
+              mma2_f8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, accumulate);
+          }
+          tc_commit_pair(&empty_bar[stage]);
+          if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
+        }
+        tc_commit_pair(&tfull_bar[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (both CTAs) =====================
+    const int q = warp - 4;                       // TMEM lane quarter of this warp
+    const int et = threadIdx.x - 128;             // 0..127 among the epilogue threads
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t stage_out = epi0 + q * 2 * kG2StageOut;
+    const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty_bar[0]), 0);
+    const bool has_bias = p.bias != nullptr;
+    const uint32_t swz = (uint32_t)(lane & 7) << 4;   // 128B swizzle: 16-byte chunk ^= row & 7
+    int acc = 0, obuf = 0;
+    uint32_t acc_phase = 0;
+
+    for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+      int tm, tn;
+      tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+      const int n0 = tn * kG2TileN;
+      const int m0 = tm * 2 * kG2RowsA + (int)cta * kG2RowsA + q * 32;   // first token of this warp
+      const int m = m0 + lane;
+      const uint32_t sw_s = vec0 + acc * (2 * kG2TileN * 4);
+      const uint32_t bias_s = sw_s + kG2TileN * 4;
+      float sxm = 0.0f;
+      if constexpr (!OUT_ACC) {
+        // stage this tile's weight scales / bias (fp32) for broadcast reads
+#pragma unroll
+        for (int i = 0; i < kG2TileN / 128; ++i) {
+          const int n = n0 + et + i * 128;
+          sts32f(sw_s + (et + i * 128) * 4, n < p.N ? __ldg(p.sw + n) : 0.0f);
+          if (has_bias) sts32f(bias_s + (et + i * 128) * 4, n < p.N ? bf16_lo(p.bias[n]) : 0.0f);
+        }
+        sxm = m < p.M ? __ldg(p.sx + m) : 0.0f;
+        named_bar_sync(1, 128);
+      }
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+
+      if constexpr (OUT_ACC) {
+#pragma unroll 1
+        for (int c = 0; c < kG2TileN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld32(lane_addr + acc * kG2TileN + c * 32, r);
+          tmem_ld_wait();
+          if (m < p.M) {
+            int32_t* dst = p.acc_out + (int64_t)m * p.N + n0 + c * 32;
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (n0 + c * 32 + i < p.N) dst[i] = (int32_t)r[i];
+          }
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < kG2TileN / kG2StoreCols; ++c) {   // 64 features per step
+          uint32_t r0[32], r1[32];
+          tmem_ld32(lane_addr + acc * kG2TileN + c * 64, r0);
+          tmem_ld32(lane_addr + acc * kG2TileN + c * 64 + 32, r1);
+          // the staging buffer we are about to overwrite was handed to TMA two steps ago
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+          tmem_ld_wait();
+          const uint32_t out = stage_out + obuf * kG2StageOut + lane * 128;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {       // 8 features -> one 16-byte chunk
+              const int col = c * 64 + h * 32 + j * 8;
+              const float4 s0 = lds128f(sw_s + col * 4), s1 = lds128f(sw_s + col * 4 + 16);
+              const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+              float bv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+              if (has_bias) {
+                const float4 b0 = lds128f(bias_s + col * 4), b1 = lds128f(bias_s + col * 4 + 16);
+                bv[0] = b0.x; bv[1] = b0.y; bv[2] = b0.z; bv[3] = b0.w;
+                bv[4] = b1.x; bv[5] = b1.y; bv[6] = b1.z; bv[7] = b1.w;
+              }
+              float v[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const uint32_t raw = h == 0 ? r0[j * 8 + e] : r1[j * 8 + e];
+                const float a = FMT == QL_INT8 ? __int2float_rn((int)raw) : __uint_as_float(raw);
+                float t = __fmul_rn(__fmul_rn(a, sxm), sv[e]);   // (acc * sa) * sb, reference :121
+                if (has_bias) t = __fadd_rn(t, bv[e]);
+                v[e] = t;
+              }
+              const uint32_t chunk = (uint32_t)(h * 4 + j) << 4;
+              sts128(out + (chunk ^ swz), pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                     pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            // rows >= M and columns >= N are clipped by the TMA unit; a box that is entirely
+            // outside is skipped, but its (empty) group is still committed so that
+            // wait_group.read<1> keeps meaning "the store two steps ago"
+            if (m0 < p.M && n0 + c * 64 < p.N)
+              tma_store_2d(&tm_y, stage_out + obuf * kG2StageOut, n0 + c * 64, m0);
+            tma_store_commit();
+          }
+          obuf ^= 1;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(tempty_leader0 + acc * 8);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (lane == 0) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc2(tmem_base, 512);
+}
+
+// ------------------------------------------------------------------ host side
+
+template <int FMT, bool OUT_ACC>
+static int launch_g2(const void* qx, const void* qw, void* y, int64_t ldy, Gemm2Params p,
+                     cudaStream_t st) {
+  auto kern = gemm2_kernel<FMT, OUT_ACC>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem) !=
+        cudaSuccess)
+      return QL_ERR_CUDA;
+    attr_set = true;
+  }
+  CUtensorMap tm_x, tm_w, tm_y;
+  if (!make_tmap_2d(&tm_x, qx, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.M, p.K, kG2BlockK, kG2RowsA) ||
+      !make_tmap_2d(&tm_w, qw, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.N, p.K, kG2BlockK, kG2RowsB))
+    return QL_ERR_CUDA;
+  if constexpr (OUT_ACC) {
+    tm_y = tm_x;  // unused by the kernel
+  } else {
+    if (!make_tmap_2d(&tm_y, y, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p.N, p.M, ldy * 2, kG2StoreCols, 32))
+      return QL_ERR_CUDA;
+  }
+  p.tiles_m = (p.M + 2 * kG2RowsA - 1) / (2 * kG2RowsA);
+  p.tiles_n = (p.N + kG2TileN - 1) / kG2TileN;
+  // keep a super-group's activations (group_m x 256 x K bytes) within ~48 MB of the 126 MB L2
+  {
+    const int64_t g = (48ll << 20) / (256ll * p.K);
+    p.group_m = (int)(g < 1 ? 1 : (g > p.tiles_m ? p.tiles_m : g));
+  }
+  const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+  // A persistent kernel must not launch more clusters than can be co-resident: a GPC with an
+  // odd number of free SMs strands one, so ask the driver instead of assuming num_sms / 2.
+  static int pairs_max = 0;
+  if (pairs_max == 0) {
+    cudaLaunchConfig_t qc = {};
+    qc.gridDim = dim3(num_sms() & ~1);
+    qc.blockDim = dim3(kG2Threads);
+    qc.dynamicSmemBytes = kG2Smem;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &qc) != cudaSuccess || n < 1) {
+      (void)cudaGetLastError();
+      n = num_sms() / 2;
+    }
+    pairs_max = n;
+    if (getenv("QL_DEBUG") != nullptr)
+      fprintf(stderr, "[qlinear_b200] gemm2: %d co-resident CTA pairs on %d SMs\n", n, num_sms());
+  }
+  const int pairs = (int)(tiles < pairs_max ? tiles : pairs_max);
+  kern<<<2 * pairs, kG2Threads, kG2Smem, st>>>(tm_x, tm_w, tm_y, p);
+  count_launch();
+  return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
+}
+
+bool gemm2_eligible(const void* y, int64_t ldy, bool out_acc) {
+  if (out_acc) return true;
+  return (reinterpret_cast<uintptr_t>(y) & 15) == 0 && ldy % 8 == 0;   // TMA store: 16-byte pitch
+}
+
+int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* sw,
+                 const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
+                 int64_t K, int fmt, cudaStream_t st) {
+  if (M == 0 || N == 0) return QL_OK;
+  Gemm2Params p;
+  p.sx = sx; p.sw = sw;
+  p.bias = static_cast<const uint16_t*>(bias);
+  p.acc_out = out_acc;
+  p.M = (int)M; p.N = (int)N; p.K = (int)K;
+  p.tiles_m = p.tiles_n = 0;
+  p.group_m = 1;
+  if (out_acc != nullptr) return launch_g2<QL_INT8, true>(qx, qw, y, ldy, p, st);
+  if (fmt == QL_INT8) return launch_g2<QL_INT8, false>(qx, qw, y, ldy, p, st);
+  return launch_g2<QL_FP8_E4M3, false>(qx, qw, y, ldy, p, st);
+}
+
+}  // namespace ql

@@ -25,6 +25,7 @@
 // INT8 accumulators are exact int32 (kind::i8, SASS UTCIMMA); FP8 accumulates in fp32
 // (kind::f8f6f4, SASS UTCQMMA).  Epilogue order is the reference's: (float(acc) * sx[m]) * sw[n].
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -42,6 +43,7 @@ struct GemmParams {
   int G;                 // scale columns (per-group) or 1
   int kb_per_g;          // 128-byte K blocks per scale group
   int tiles_n, tiles_m;
+  int group_m;           // token tiles per rasterisation super-group (common.cuh tile_coords)
 };
 
 constexpr int kGemmThreads = 256;
@@ -123,7 +125,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int tn = tile % p.tiles_n, tm = tile / p.tiles_n;
+        int tm, tn;
+        tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::stage;
@@ -222,7 +225,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
     };
 
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int tn = tile % p.tiles_n, tm = tile / p.tiles_n;
+      int tm, tn;
+      tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
       const int nq0 = tn * kTileN + q * 32;
       const int n = nq0 + lane;
       const bool n_ok = n < p.N;
@@ -353,18 +357,22 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// 2-D uint8 tensor [rows, K] (K contiguous), box = {128 K-bytes, box_rows}, 128B swizzle,
-// out-of-bounds rows read as zero.
-static bool make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t K, int box_rows) {
+bool make_tmap_2d(CUtensorMap* tm, const void* base, CUtensorMapDataType dt, int64_t inner,
+                  int64_t outer, int64_t row_stride_bytes, int box_inner, int box_outer) {
   EncodeTiledFn fn = encode_fn();
   if (fn == nullptr) return false;
-  cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
-  cuuint64_t gstride[1] = {(cuuint64_t)K};
-  cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)box_rows};
+  cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t gstride[1] = {(cuuint64_t)row_stride_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
-  return fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), gdim, gstride, box,
-            estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  return fn(tm, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// 2-D uint8 tensor [rows, K] (K contiguous), box = {128 K-bytes, box_rows}
+static bool make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t K, int box_rows) {
+  return make_tmap_2d(tm, base, CU_TENSOR_MAP_DATA_TYPE_UINT8, K, rows, K, kBlockK, box_rows);
 }
 
 template <int FMT, bool GROUPED, int BT, bool OUT_ACC>
@@ -383,6 +391,10 @@ static int launch_cfg(const void* qx, const void* qw, GemmParams p, cudaStream_t
     return QL_ERR_CUDA;
   p.tiles_n = (p.N + kTileN - 1) / kTileN;
   p.tiles_m = (p.M + BT - 1) / BT;
+  {
+    const int64_t g = (48ll << 20) / ((int64_t)BT * p.K);   // activations of a super-group stay in L2
+    p.group_m = (int)(g < 1 ? 1 : (g > p.tiles_m ? p.tiles_m : g));
+  }
   const int64_t tiles = (int64_t)p.tiles_n * p.tiles_m;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   kern<<<grid, kGemmThreads, Cfg::smem_bytes, st>>>(tm_w, tm_x, p);
@@ -415,10 +427,28 @@ static int launch_bt(const void* qx, const void* qw, const GemmParams& p, cudaSt
   }
 }
 
+// Kernel choice.  The CTA-pair kernel needs enough 256x256 tiles to occupy the 74 SM pairs;
+// below that the single-CTA kernel's 128 x {32..256} tiles spread the work over more SMs.
+// QL_FORCE_GEMM=1|2 (read once) pins the choice for sweeps and tests.
+int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group) {
+  (void)K;
+  if (group > 0) return 1;
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("QL_FORCE_GEMM");
+    forced = (e != nullptr && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : 0;
+  }
+  if (forced) return forced;
+  const int64_t tiles2 = ((M + 255) / 256) * ((N + 255) / 256);
+  return (M >= 512 && tiles2 >= 32) ? 2 : 1;
+}
+
 int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw,
                 const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
                 int64_t K, int fmt, int64_t group, cudaStream_t st) {
   if (M == 0 || N == 0) return QL_OK;
+  if (gemm_kernel_choice(M, N, K, group) == 2 && gemm2_eligible(y, ldy, out_acc != nullptr))
+    return launch_gemm2(qx, sx, qw, sw, bias, y, ldy, out_acc, M, N, K, fmt, st);
   GemmParams p;
   p.sx = sx; p.sw = sw;
   p.bias = static_cast<const uint16_t*>(bias);
@@ -429,6 +459,7 @@ int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw
   p.G = group > 0 ? (int)(K / group) : 1;
   p.kb_per_g = group > 0 ? (int)(group / kBlockK) : 1;
   p.tiles_n = p.tiles_m = 0;
+  p.group_m = 1;
   if (out_acc != nullptr) return launch_bt<QL_INT8, false, true>(qx, qw, p, st);
   if (fmt == QL_INT8)
     return group > 0 ? launch_bt<QL_INT8, true, false>(qx, qw, p, st)

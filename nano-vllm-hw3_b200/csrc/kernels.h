@@ -2,6 +2,7 @@
 // The public surface is include/qlinear_b200.h; these take validated arguments.
 #pragma once
 
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -24,6 +25,19 @@ int launch_gemv(const void* x, int64_t ldx, const void* qx_pre, const float* sx_
 int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw,
                 const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
                 int64_t K, int fmt, int64_t group, cudaStream_t st);
+
+// CTA-pair (cta_group::2) tcgen05 GEMM for prefill-sized M, per-row scales only.
+int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* sw,
+                 const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
+                 int64_t K, int fmt, cudaStream_t st);
+bool gemm2_eligible(const void* y, int64_t ldy, bool out_acc);
+// Which GEMM kernel launch_gemm picks: 1 = single-CTA weight-stationary, 2 = CTA pair.
+int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group);
+
+// 2-D tiled TMA descriptor: tensor [outer, inner] with `row_stride_bytes` between rows, box
+// {box_inner, box_outer} elements, 128-byte swizzle, out-of-bounds reads as zero / writes clipped.
+bool make_tmap_2d(CUtensorMap* tm, const void* base, CUtensorMapDataType dt, int64_t inner,
+                  int64_t outer, int64_t row_stride_bytes, int box_inner, int box_outer);
 
 int num_sms();
 

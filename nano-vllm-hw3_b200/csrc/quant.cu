@@ -9,18 +9,25 @@
 
 namespace ql {
 
-// One warp per row.  Rows of up to NV*256 elements stay in registers between the amax pass and
-// the quantise pass (NV = 4 -> K <= 1024, NV = 16 -> K <= 4096); NV = 0 re-reads the row, which
-// then comes from L1/L2 (a row is at most a few tens of KB).
-template <int FMT, int NV>
-__global__ void __launch_bounds__(256)
+// WPR warps own one row (128-thread blocks, 4 / WPR rows per block).  A lane keeps NV 16-byte
+// vectors (8 bf16 each) in registers between the amax pass and the quantise pass, so a row of
+// up to WPR * NV * 256 elements is read exactly once.  NV is kept <= 8 (about 64 registers) so
+// that 6+ blocks are resident per SM and the grid covers the machine in about one wave; the
+// cross-warp amax (WPR > 1) goes through shared memory.  NV = 0: rows longer than 16 K elements
+// are read twice (the second read comes from L2).
+template <int FMT, int NV, int WPR>
+__global__ void __launch_bounds__(128)
 quant_rows_kernel(const uint16_t* __restrict__ x, int64_t M, int K, int64_t ldx,
                   uint8_t* __restrict__ q, float* __restrict__ s) {
-  const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= M) return;
-  const uint4* xr = reinterpret_cast<const uint4*>(x + row * ldx);
-  uint2* qr = reinterpret_cast<uint2*>(q + row * (int64_t)K);
+  __shared__ float red[4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int ROWS = 4 / WPR;
+  const int64_t row = (int64_t)blockIdx.x * ROWS + warp / WPR;
+  const int part = warp % WPR;                      // this warp's slice of the row
+  const bool live = row < M;
+  const int64_t rowc = live ? row : 0;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + rowc * ldx);
+  uint2* qr = reinterpret_cast<uint2*>(q + rowc * (int64_t)K);
   const int nvec = K >> 3;
   constexpr float qmax = Fmt<FMT>::qmax;
 
@@ -29,25 +36,39 @@ quant_rows_kernel(const uint16_t* __restrict__ x, int64_t M, int K, int64_t ldx,
     uint4 v[NV];
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
-      const int idx = lane + i * 32;
-      v[i] = idx < nvec ? __ldg(xr + idx) : make_uint4(0, 0, 0, 0);
+      const int idx = (i * WPR + part) * 32 + lane;
+      v[i] = (live && idx < nvec) ? ldg_stream(xr + idx) : make_uint4(0, 0, 0, 0);
     }
 #pragma unroll
     for (int i = 0; i < NV; ++i) amax = fmaxf(amax, amax8(v[i]));
-    amax = fmaxf(warp_max(amax), 1e-8f);
+    amax = warp_max(amax);
+    if constexpr (WPR > 1) {
+      if (lane == 0) red[warp] = amax;
+      __syncthreads();
+      const int w0 = (warp / WPR) * WPR;
+#pragma unroll
+      for (int i = 0; i < WPR; ++i) amax = fmaxf(amax, red[w0 + i]);
+    }
+    amax = fmaxf(amax, 1e-8f);
     const float inv = __fdiv_rn(qmax, amax);
-    if (lane == 0) s[row] = __fdiv_rn(amax, qmax);
+    if (live && part == 0 && lane == 0) s[row] = __fdiv_rn(amax, qmax);
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
-      const int idx = lane + i * 32;
-      if (idx < nvec) qr[idx] = quant8_mul<FMT>(v[i], inv);
+      const int idx = (i * WPR + part) * 32 + lane;
+      if (live && idx < nvec) qr[idx] = quant8_mul<FMT>(v[i], inv);
     }
   } else {
-    for (int idx = lane; idx < nvec; idx += 32) amax = fmaxf(amax, amax8(__ldg(xr + idx)));
-    amax = fmaxf(warp_max(amax), 1e-8f);
+    static_assert(NV > 0 || WPR == 4, "long rows use the whole block");
+    if (live)
+      for (int idx = threadIdx.x; idx < nvec; idx += 128) amax = fmaxf(amax, amax8(__ldg(xr + idx)));
+    amax = warp_max(amax);
+    if (lane == 0) red[warp] = amax;
+    __syncthreads();
+    amax = fmaxf(fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3])), 1e-8f);
     const float inv = __fdiv_rn(qmax, amax);
-    if (lane == 0) s[row] = __fdiv_rn(amax, qmax);
-    for (int idx = lane; idx < nvec; idx += 32) qr[idx] = quant8_mul<FMT>(__ldg(xr + idx), inv);
+    if (live && threadIdx.x == 0) s[row] = __fdiv_rn(amax, qmax);
+    if (live)
+      for (int idx = threadIdx.x; idx < nvec; idx += 128) qr[idx] = quant8_mul<FMT>(__ldg(xr + idx), inv);
   }
 }
 
@@ -152,17 +173,23 @@ static int launch_quant_rows_fmt(const void* x, int64_t M, int64_t K, int64_t ld
                                  float* s, cudaStream_t st) {
   const auto* xp = static_cast<const uint16_t*>(x);
   auto* qp = static_cast<uint8_t*>(q);
-  const unsigned blocks = (unsigned)((M + 7) / 8);
   const bool vec_ok = (K % 8 == 0) && (ldx % 8 == 0) && ((uintptr_t)x % 16 == 0) &&
                       ((uintptr_t)q % 8 == 0);
+  const int K_ = (int)K;
+#define QL_QROWS(NV, WPR)                                                                   \
+  quant_rows_kernel<FMT, NV, WPR><<<(unsigned)((M + (4 / WPR) - 1) / (4 / WPR)), 128, 0, st>>>( \
+      xp, M, K_, ldx, qp, s)
   if (!vec_ok)
-    quant_rows_scalar_kernel<FMT><<<blocks, 256, 0, st>>>(xp, M, (int)K, ldx, qp, s);
-  else if (K <= 1024)
-    quant_rows_kernel<FMT, 4><<<blocks, 256, 0, st>>>(xp, M, (int)K, ldx, qp, s);
-  else if (K <= 4096)
-    quant_rows_kernel<FMT, 16><<<blocks, 256, 0, st>>>(xp, M, (int)K, ldx, qp, s);
-  else
-    quant_rows_kernel<FMT, 0><<<blocks, 256, 0, st>>>(xp, M, (int)K, ldx, qp, s);
+    quant_rows_scalar_kernel<FMT><<<(unsigned)((M + 7) / 8), 256, 0, st>>>(xp, M, K_, ldx, qp, s);
+  else if (K <= 1024) QL_QROWS(4, 1);
+  else if (K <= 2048) QL_QROWS(8, 1);
+  else if (K <= 3072) QL_QROWS(6, 2);
+  else if (K <= 4096) QL_QROWS(8, 2);
+  else if (K <= 8192) QL_QROWS(8, 4);
+  else if (K <= 12288) QL_QROWS(12, 4);
+  else if (K <= 16384) QL_QROWS(16, 4);
+  else QL_QROWS(0, 4);
+#undef QL_QROWS
   count_launch();
   return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
 }

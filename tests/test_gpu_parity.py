@@ -219,6 +219,60 @@ def test_gemm_groups_vs_oracle(ext, dn, g, M, N, K):
         assert_close_fp(bits(y), yo)
 
 
+# ------------------------------------------------------------------ prefill regime: CTA-pair kernel
+
+PAIR_SHAPES = [(512, 4096, 128), (1024, 2048, 1024), (1000, 2072, 384), (777, 4096, 256),
+               (4096, 1024, 2048), (2304, 1032, 640)]
+
+
+@pytest.mark.parametrize("M,N,K", PAIR_SHAPES)
+def test_gemm_pair_i8_acc_bit_exact(ext, M, N, K):
+    """cta_group::2 kernel (256x256 pair tiles): raw int32 accumulators, tails in M and N."""
+    assert ext.linear_path(M, N, K) == "gemm_tcgen05_2cta"
+    qx, qw = rand_i8((M, K), M * 5 + K), rand_i8((N, K), N * 11 + K)
+    qx[-1] = 127
+    qw[-1] = -127
+    qx[M // 2] = -127
+    qw[N // 2 + 1] = -127
+    acc = ext.gemm_i8_acc(qx.cuda(), qw.cuda())
+    ref = orc.gemm_i8_acc(qx.numpy(), qw.numpy())
+    assert np.array_equal(acc.cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("bias", [False, True])
+@pytest.mark.parametrize("M,N,K", PAIR_SHAPES)
+def test_gemm_pair_rows_vs_oracle(ext, dn, bias, M, N, K):
+    assert ext.linear_path(M, N, K) == "gemm_tcgen05_2cta"
+    x, w = rand_bf16((M, K), M + N + 3), rand_bf16((N, K), K + N + 3, 0.02)
+    b = rand_bf16((N,), 21) if bias else None
+    qx, sx = orc.quant_rows(bits(x), FMT[dn])
+    qw, sw = orc.quant_rows(bits(w), FMT[dn])
+    y = ext.gemm_w8a8(dev(qx, DT[dn]), dev(sx, torch.float32), dev(qw, DT[dn]), dev(sw, torch.float32),
+                      None if b is None else b.cuda(), DT[dn])
+    yo = orc.gemm_rows(qx, sx, qw, sw, None if b is None else bits(b), FMT[dn])
+    if dn == "i8":
+        assert np.array_equal(bits(y), yo)
+    else:
+        assert_close_fp(bits(y), yo)
+
+
+def test_gemm_pair_strided_output_and_unaligned_fallback(ext):
+    """ql_linear with a strided y (ldy > N) goes through the TMA-store epilogue; an output whose
+    pitch is not a multiple of 16 bytes falls back to the single-CTA kernel.  Both bit-exact."""
+    M, N, K = 1024, 2048, 512
+    x, w = rand_bf16((M, K), 5), rand_bf16((N, K), 6, 0.02)
+    qw, sw = orc.quant_rows(bits(w), orc.INT8)
+    qx, sx = orc.quant_rows(bits(x), orc.INT8)
+    yo = orc.gemm_rows(qx, sx, qw, sw, None, orc.INT8)
+    for pitch in (N + 64, N + 3):
+        buf = torch.full((M, pitch), 7.0, dtype=torch.bfloat16, device="cuda")
+        out = buf[:, :N]
+        ext.linear(x.cuda(), dev(qw, torch.int8), dev(sw, torch.float32), None, torch.int8, 0, out=out)
+        assert np.array_equal(bits(out.contiguous()), yo)
+        assert bool((buf[:, N:] == 7.0).all())          # nothing written past column N
+
+
 # ------------------------------------------------------------------ decode regime: fused GEMV
 
 @pytest.mark.parametrize("dn", ["i8", "f8"])
