@@ -17,13 +17,14 @@
 // to the TMA store engine (cp.async.bulk.tensor ... global.shared::cta).  No per-element
 // address arithmetic, no transposition, stores fully coalesced by the TMA unit.
 //
-// Pipeline per CTA (256 threads; both CTAs of a pair run the same roles except the MMA issue):
+// Pipeline per CTA (384 threads; both CTAs of a pair run the same roles except the MMA issue):
 //   warp 0 / lane 0  TMA producer: own A rows + own half of B per K block -> STAGES-deep ring;
 //                    completion bytes are counted on the LEADER CTA's `full` barrier
 //   warp 1 / lane 0  (leader CTA only) MMA issuer; tcgen05.commit multicast to both CTAs frees
 //                    the ring slot (`empty`) and publishes the accumulator (`tfull`)
 //   warp 2           TMEM allocator (512 columns = two 256-column accumulators)
-//   warps 4-7        epilogue (TMEM -> registers -> scales -> bf16 -> smem -> TMA store);
+//   warps 4-11       epilogue (TMEM -> registers -> scales -> bf16 -> smem -> TMA store), two
+//                    warps per SM sub-partition so their tcgen05.ld / fence / store waits overlap;
 //                    arrives on the leader's `tempty` when an accumulator has been drained
 #include <cuda.h>
 #include <stdio.h>
@@ -44,7 +45,8 @@ struct Gemm2Params {
   int group_m;           // token tiles per rasterisation super-group
 };
 
-constexpr int kG2Threads = 256;
+constexpr int kG2Threads = 384;   // 4 control warps + 8 epilogue warps
+constexpr int kG2EpiWarps = 8;
 constexpr int kG2RowsA = 128;    // token rows per CTA (UMMA M = 256 per pair)
 constexpr int kG2TileN = 256;    // features per pair tile (UMMA N)
 constexpr int kG2RowsB = 128;    // weight rows staged per CTA (half of the tile)
@@ -55,8 +57,8 @@ constexpr int kG2StageB = kG2RowsB * kG2BlockK;
 constexpr int kG2Stage = kG2StageA + kG2StageB;                 // 32 KB
 constexpr int kG2StoreCols = 64;                                // bf16 columns per TMA store box (128 B)
 constexpr int kG2StageOut = 32 * kG2StoreCols * 2;              // 4 KB: [32 tokens][64 features]
-constexpr int kG2EpiSmem = 4 * 2 * kG2StageOut;                 // 4 warps x 2 buffers
-constexpr int kG2VecSmem = 2 * 2 * kG2TileN * 4;                // sw / bias tiles, double buffered
+constexpr int kG2EpiSmem = kG2EpiWarps * kG2StageOut;            // one staging tile per epilogue warp
+constexpr int kG2VecSmem = 2 * 2 * kG2TileN * 4;                // sw / bias tiles (fp32), double buffered
 constexpr int kG2Smem = kG2Stages * kG2Stage + kG2EpiSmem + kG2VecSmem + 256 + 1024;
 
 // ---- cluster / peer helpers -----------------------------------------------------------------
@@ -171,7 +173,7 @@ __device__ __forceinline__ void sts32f(uint32_t addr, float v) {
   asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 
-template <int FMT, bool OUT_ACC>
+template <int FMT, bool OUT_ACC, bool HAS_BIAS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kG2Threads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
              const __grid_constant__ CUtensorMap tm_y, const Gemm2Params p) {
@@ -205,7 +207,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull_bar[i], 1);   // one multicast tcgen05.commit
-      mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps x 2 CTAs
+      mbar_init(&tempty_bar[i], 2 * kG2EpiWarps);  // epilogue warps of both CTAs
     }
     mbar_fence_init();
   }
@@ -279,73 +281,77 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue (both CTAs) =====================
-    const int q = warp - 4;                       // TMEM lane quarter of this warp
-    const int et = threadIdx.x - 128;             // 0..127 among the epilogue threads
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-    const uint32_t stage_out = epi0 + q * 2 * kG2StageOut;
+    // ===================== epilogue (both CTAs, 8 warps) =====================
+    // Warp ew reads TMEM lane quarter q = ew % 4 (hardware: a warp may only touch lanes
+    // 32*(warp%4)..+31) and column half ew / 4, i.e. a [32 tokens][128 features] block per tile
+    // in two 64-column steps.  Two warps per SM sub-partition: while one waits on tcgen05.ld,
+    // the proxy fence or the TMA store engine, the other issues.
+    const int ew = warp - 4;
+    const int q = ew & 3, half = ew >> 2;
+    const int et = threadIdx.x - 128;             // 0..255 among the epilogue threads
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16) + half * 128;
+    const uint32_t stage_out = epi0 + ew * kG2StageOut;
     const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty_bar[0]), 0);
-    const bool has_bias = p.bias != nullptr;
     const uint32_t swz = (uint32_t)(lane & 7) << 4;   // 128B swizzle: 16-byte chunk ^= row & 7
-    int acc = 0, obuf = 0;
+    const uint32_t out = stage_out + lane * 128;
+    int acc = 0;
     uint32_t acc_phase = 0;
 
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       int tm, tn;
       tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
-      const int n0 = tn * kG2TileN;
+      const int n0 = tn * kG2TileN + half * 128;                          // first feature of this warp
       const int m0 = tm * 2 * kG2RowsA + (int)cta * kG2RowsA + q * 32;   // first token of this warp
       const int m = m0 + lane;
-      const uint32_t sw_s = vec0 + acc * (2 * kG2TileN * 4);
-      const uint32_t bias_s = sw_s + kG2TileN * 4;
       float sxm = 0.0f;
+      const uint32_t sw_s = vec0 + acc * (2 * kG2TileN * 4) + half * 128 * 4;
+      const uint32_t bias_s = sw_s + kG2TileN * 4;
       if constexpr (!OUT_ACC) {
-        // stage this tile's weight scales / bias (fp32) for broadcast reads
-#pragma unroll
-        for (int i = 0; i < kG2TileN / 128; ++i) {
-          const int n = n0 + et + i * 128;
-          sts32f(sw_s + (et + i * 128) * 4, n < p.N ? __ldg(p.sw + n) : 0.0f);
-          if (has_bias) sts32f(bias_s + (et + i * 128) * 4, n < p.N ? bf16_lo(p.bias[n]) : 0.0f);
-        }
+        // stage this tile's weight scales / bias (fp32) for broadcast LDS.128 reads: one
+        // column per epilogue thread, double-buffered by accumulator index
+        const int n = tn * kG2TileN + et;
+        sts32f(vec0 + acc * (2 * kG2TileN * 4) + et * 4, n < p.N ? __ldg(p.sw + n) : 0.0f);
+        if constexpr (HAS_BIAS)
+          sts32f(vec0 + acc * (2 * kG2TileN * 4) + kG2TileN * 4 + et * 4,
+                 n < p.N ? bf16_lo(p.bias[n]) : 0.0f);
         sxm = m < p.M ? __ldg(p.sx + m) : 0.0f;
-        named_bar_sync(1, 128);
+        named_bar_sync(1, 32 * kG2EpiWarps);
       }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
 
       if constexpr (OUT_ACC) {
 #pragma unroll 1
-        for (int c = 0; c < kG2TileN / 32; ++c) {
+        for (int c = 0; c < 4; ++c) {
           uint32_t r[32];
           tmem_ld32(lane_addr + acc * kG2TileN + c * 32, r);
           tmem_ld_wait();
           if (m < p.M) {
-            int32_t* dst = p.acc_out + (int64_t)m * p.N + n0 + c * 32;
+            const int nb = n0 + c * 32;
+            int32_t* dst = p.acc_out + (int64_t)m * p.N + nb;
 #pragma unroll
             for (int i = 0; i < 32; ++i)
-              if (n0 + c * 32 + i < p.N) dst[i] = (int32_t)r[i];
+              if (nb + i < p.N) dst[i] = (int32_t)r[i];
           }
         }
       } else {
 #pragma unroll 1
-        for (int c = 0; c < kG2TileN / kG2StoreCols; ++c) {   // 64 features per step
+        for (int c = 0; c < 2; ++c) {                 // 64 features per step
+          const int nc = n0 + c * 64;                 // first feature of this step
           uint32_t r0[32], r1[32];
           tmem_ld32(lane_addr + acc * kG2TileN + c * 64, r0);
           tmem_ld32(lane_addr + acc * kG2TileN + c * 64 + 32, r1);
-          // the staging buffer we are about to overwrite was handed to TMA two steps ago
-          if (lane == 0) tma_store_wait_read<1>();
-          __syncwarp();
           tmem_ld_wait();
-          const uint32_t out = stage_out + obuf * kG2StageOut + lane * 128;
+          uint32_t pk[32];                            // 64 bf16 results of this token
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {       // 8 features -> one 16-byte chunk
-              const int col = c * 64 + h * 32 + j * 8;
+            for (int j = 0; j < 4; ++j) {             // 8 features -> one 16-byte chunk
+              const int col = c * 64 + h * 32 + j * 8;   // column inside this warp's 128
               const float4 s0 = lds128f(sw_s + col * 4), s1 = lds128f(sw_s + col * 4 + 16);
               const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
               float bv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-              if (has_bias) {
+              if constexpr (HAS_BIAS) {
                 const float4 b0 = lds128f(bias_s + col * 4), b1 = lds128f(bias_s + col * 4 + 16);
                 bv[0] = b0.x; bv[1] = b0.y; bv[2] = b0.z; bv[3] = b0.w;
                 bv[4] = b1.x; bv[5] = b1.y; bv[6] = b1.z; bv[7] = b1.w;
@@ -356,25 +362,29 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
                 const uint32_t raw = h == 0 ? r0[j * 8 + e] : r1[j * 8 + e];
                 const float a = FMT == QL_INT8 ? __int2float_rn((int)raw) : __uint_as_float(raw);
                 float t = __fmul_rn(__fmul_rn(a, sxm), sv[e]);   // (acc * sa) * sb, reference :121
-                if (has_bias) t = __fadd_rn(t, bv[e]);
+                if constexpr (HAS_BIAS) t = __fadd_rn(t, bv[e]);
                 v[e] = t;
               }
-              const uint32_t chunk = (uint32_t)(h * 4 + j) << 4;
-              sts128(out + (chunk ^ swz), pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
-                     pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+#pragma unroll
+              for (int e = 0; e < 4; ++e) pk[(h * 4 + j) * 4 + e] = pack_bf16x2(v[2 * e], v[2 * e + 1]);
             }
           }
+          // the staging tile is rewritten: the TMA store issued from it one step ago (a whole
+          // step of arithmetic earlier) must have finished reading shared memory
+          if (lane == 0) tma_store_wait_read<0>();
+          __syncwarp();
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch)
+            sts128(out + (((uint32_t)ch << 4) ^ swz), pk[ch * 4], pk[ch * 4 + 1], pk[ch * 4 + 2],
+                   pk[ch * 4 + 3]);
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            // rows >= M and columns >= N are clipped by the TMA unit; a box that is entirely
-            // outside is skipped, but its (empty) group is still committed so that
-            // wait_group.read<1> keeps meaning "the store two steps ago"
-            if (m0 < p.M && n0 + c * 64 < p.N)
-              tma_store_2d(&tm_y, stage_out + obuf * kG2StageOut, n0 + c * 64, m0);
+            // rows >= M and columns >= N are clipped by the TMA unit; a box entirely outside
+            // the tensor is not issued
+            if (m0 < p.M && nc < p.N) tma_store_2d(&tm_y, stage_out, nc, m0);
             tma_store_commit();
           }
-          obuf ^= 1;
         }
       }
       tc_fence_before();
@@ -392,10 +402,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
 
 // ------------------------------------------------------------------ host side
 
-template <int FMT, bool OUT_ACC>
+template <int FMT, bool OUT_ACC, bool HAS_BIAS>
 static int launch_g2(const void* qx, const void* qw, void* y, int64_t ldy, Gemm2Params p,
                      cudaStream_t st) {
-  auto kern = gemm2_kernel<FMT, OUT_ACC>;
+  auto kern = gemm2_kernel<FMT, OUT_ACC, HAS_BIAS>;
   static bool attr_set = false;
   if (!attr_set) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem) !=
@@ -444,7 +454,8 @@ static int launch_g2(const void* qx, const void* qw, void* y, int64_t ldy, Gemm2
   return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
 }
 
-bool gemm2_eligible(const void* y, int64_t ldy, bool out_acc) {
+bool gemm2_eligible(const void* y, int64_t ldy, const void* sw, const void* bias, bool out_acc) {
+  (void)sw; (void)bias;
   if (out_acc) return true;
   return (reinterpret_cast<uintptr_t>(y) & 15) == 0 && ldy % 8 == 0;   // TMA store: 16-byte pitch
 }
@@ -460,9 +471,12 @@ int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* s
   p.M = (int)M; p.N = (int)N; p.K = (int)K;
   p.tiles_m = p.tiles_n = 0;
   p.group_m = 1;
-  if (out_acc != nullptr) return launch_g2<QL_INT8, true>(qx, qw, y, ldy, p, st);
-  if (fmt == QL_INT8) return launch_g2<QL_INT8, false>(qx, qw, y, ldy, p, st);
-  return launch_g2<QL_FP8_E4M3, false>(qx, qw, y, ldy, p, st);
+  if (out_acc != nullptr) return launch_g2<QL_INT8, true, false>(qx, qw, y, ldy, p, st);
+  if (fmt == QL_INT8)
+    return bias ? launch_g2<QL_INT8, false, true>(qx, qw, y, ldy, p, st)
+                : launch_g2<QL_INT8, false, false>(qx, qw, y, ldy, p, st);
+  return bias ? launch_g2<QL_FP8_E4M3, false, true>(qx, qw, y, ldy, p, st)
+              : launch_g2<QL_FP8_E4M3, false, false>(qx, qw, y, ldy, p, st);
 }
 
 }  // namespace ql

@@ -447,7 +447,7 @@ int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw
                 const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
                 int64_t K, int fmt, int64_t group, cudaStream_t st) {
   if (M == 0 || N == 0) return QL_OK;
-  if (gemm_kernel_choice(M, N, K, group) == 2 && gemm2_eligible(y, ldy, out_acc != nullptr))
+  if (gemm_kernel_choice(M, N, K, group) == 2 && gemm2_eligible(y, ldy, sw, bias, out_acc != nullptr))
     return launch_gemm2(qx, sx, qw, sw, bias, y, ldy, out_acc, M, N, K, fmt, st);
   GemmParams p;
   p.sx = sx; p.sw = sw;

@@ -30,7 +30,7 @@ int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw
 int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* sw,
                  const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
                  int64_t K, int fmt, cudaStream_t st);
-bool gemm2_eligible(const void* y, int64_t ldy, bool out_acc);
+bool gemm2_eligible(const void* y, int64_t ldy, const void* sw, const void* bias, bool out_acc);
 // Which GEMM kernel launch_gemm picks: 1 = single-CTA weight-stationary, 2 = CTA pair.
 int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group);
 

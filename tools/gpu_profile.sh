@@ -11,7 +11,7 @@ tail -1 gpurun_out/plain_$tag.log
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s ${SKIP:-672} -c 448 --csv \
     --log-file gpurun_out/launches_$tag.csv $CMD > gpurun_out/ncu_list_$tag.log 2>&1
 echo "ncu list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gemm_kernel|gemv_kernel|quant_rows' -s ${SKIP:-672} -c 8 \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'gemm|gemv' -s ${SKIP:-672} -c 8 \
     -o gpurun_out/prof_$tag -f $CMD > gpurun_out/ncu_full_$tag.log 2>&1
 echo "ncu full rc=$?"
 ls -la gpurun_out
