@@ -76,22 +76,81 @@ def flops_bytes(M, shapes, group=0):
 # ------------------------------------------------------------------ clocks sampler
 
 class ClockSampler:
+    """SM clock + throttle reasons sampled DURING the timed regions.  NVML in a background thread
+    (2 ms period: the default run times only tens of milliseconds, far below nvidia-smi's start-up
+    time); falls back to the profiling recipe's `nvidia-smi -lms` process when NVML is unusable."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, dev_index: int):
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
-        self.p = None
+        import threading
+        self.samples = []           # (sm_mhz, reasons bitmask, power_w)
+        self.sm_max = None
+        self.mode = None
+        self._stop = threading.Event()
+        self.p = self.f = self.t = None
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100", "-i", str(dev_index)], stdout=self.f,
-                                      stderr=subprocess.DEVNULL)
-        except OSError:
-            self.p = None
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = dev_index
+            if vis:
+                tok = vis.split(",")[dev_index].strip()
+                phys = int(tok) if tok.isdigit() else None
+                h = pynvml.nvmlDeviceGetHandleByUUID(tok) if phys is None else pynvml.nvmlDeviceGetHandleByIndex(phys)
+            else:
+                h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            self._nv, self._h = pynvml, h
+            self.mode = "nvml"
+            self.t = threading.Thread(target=self._run, daemon=True)
+            self.t.start()
+        except Exception:
+            self.mode = None
+        if self.mode is None:
+            try:
+                self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+                self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                           "-lms", "100", "-i", str(dev_index)], stdout=self.f,
+                                          stderr=subprocess.DEVNULL)
+                self.mode = "nvidia-smi"
+            except OSError:
+                self.p = None
+
+    def _run(self):
+        nv, h = self._nv, self._h
+        while not self._stop.is_set():
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h) if hasattr(
+                    nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                except Exception:
+                    pw = 0.0
+                self.samples.append((float(sm), int(rs), pw))
+            except Exception:
+                pass
+            time.sleep(0.002)
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "sampler": self.mode}
+        if self.mode == "nvml":
+            self._stop.set()
+            self.t.join(timeout=2)
+            nv = self._nv
+            bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                    "sw_power_cap": 0x4}
+            if self.samples:
+                s = sorted(v[0] for v in self.samples)
+                mask = 0
+                for v in self.samples:
+                    mask |= v[1]
+                out.update(sm_mhz=s[len(s) // 2], sm_max_mhz=self.sm_max,
+                           reasons=sorted(n for n, b in bits.items() if mask & b),
+                           samples=len(s), power_w_max=max(v[2] for v in self.samples))
+            return out
         if self.p is None:
             return out
         self.p.terminate()

@@ -73,6 +73,11 @@ QL_API int ql_device_check(void);
  * gpu_launches and for tests that assert the CUDA path -- not a fallback -- ran). */
 QL_API uint64_t ql_launch_count(void);
 
+/* Debug aid (tools/trace_skinny.py): while a device buffer of 16 int64 is registered, CTA 0 of
+ * the decode kernel stores clock64() stamps of its pipeline phases into it.  NULL switches it
+ * off (the default).  Not part of the reference-facing surface. */
+QL_API void ql_debug_set_trace(void* device_buf16_i64);
+
 /*
  * Per-row (per-token) symmetric quantiser.
  * Replaces per_row_quant / _per_row_quant_kernel, nanovllm/utils/quantization.py:13-51,147-163:

@@ -46,6 +46,18 @@ static bool aligned(const void* p, uintptr_t a) { return ((uintptr_t)p % a) == 0
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// M <= 16: one launch, quantiser fused.  The cluster split-K tcgen05 kernel when a split plan
+// fits, the mma.sync GEMV otherwise.
+static int decode_linear(const void* x, int64_t ldx, const void* qw, const float* sw,
+                         const void* bias, void* y, int64_t ldy, int64_t M, int64_t N, int64_t K,
+                         int fmt, int64_t group, cudaStream_t st) {
+  if (skinny_fused_ok(M, N, K, group)) {
+    const int r = launch_skinny_fused(x, ldx, qw, sw, bias, y, ldy, M, N, K, fmt, group, st);
+    if (r != QL_ERR_BAD_SHAPE) return r;
+  }
+  return launch_gemv(x, ldx, nullptr, nullptr, qw, sw, bias, y, ldy, M, N, K, fmt, group, st);
+}
+
 }  // namespace ql
 
 using namespace ql;
@@ -69,6 +81,8 @@ const char* ql_status_string(int status) {
 }
 
 int ql_device_check(void) { return check_arch(); }
+
+void ql_debug_set_trace(void* device_buf16_i64) { set_skinny_trace(device_buf16_i64); }
 
 uint64_t ql_launch_count(void) { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
 
@@ -121,6 +135,11 @@ int ql_gemm_w8a8(const void* qx, const float* sx, const void* qw, const float* s
   if (!qx || !sx || !qw || !sw || !y) return QL_ERR_NULL;
   if (!aligned(qx, 16) || !aligned(qw, 16)) return QL_ERR_MISALIGNED;  // TMA global address
   if (int e = check_arch()) return e;
+  if (skinny_ok(M, N, K, group)) {
+    const int r = launch_skinny(qx, sx, qw, sw, bias, y, ldy, nullptr, M, N, K, fmt, group,
+                                (cudaStream_t)stream);
+    if (r != QL_ERR_BAD_SHAPE) return r;   // BAD_SHAPE: no split plan fits, use the tiled GEMM
+  }
   return launch_gemm(qx, sx, qw, sw, bias, y, ldy, nullptr, M, N, K, fmt, group,
                      (cudaStream_t)stream);
 }
@@ -132,6 +151,11 @@ int ql_gemm_i8_acc(const void* qx, const void* qw, int32_t* acc, int64_t M, int6
   if (!qx || !qw || !acc) return QL_ERR_NULL;
   if (!aligned(qx, 16) || !aligned(qw, 16)) return QL_ERR_MISALIGNED;
   if (int e = check_arch()) return e;
+  if (skinny_ok(M, N, K, 0)) {
+    const int r = launch_skinny(qx, nullptr, qw, nullptr, nullptr, nullptr, N, acc, M, N, K, QL_INT8,
+                                0, (cudaStream_t)stream);
+    if (r != QL_ERR_BAD_SHAPE) return r;
+  }
   return launch_gemm(qx, nullptr, qw, nullptr, nullptr, nullptr, N, acc, M, N, K, QL_INT8, 0,
                      (cudaStream_t)stream);
 }
@@ -145,8 +169,7 @@ int ql_gemv_w8a8(const void* x, int64_t ldx, const void* qw, const float* sw, co
   if (!x || !qw || !sw || !y) return QL_ERR_NULL;
   if (!aligned(x, 16) || ldx % 8 != 0 || !aligned(qw, 16)) return QL_ERR_MISALIGNED;
   if (int e = check_arch()) return e;
-  return launch_gemv(x, ldx, nullptr, nullptr, qw, sw, bias, y, ldy, M, N, K, fmt, group,
-                     (cudaStream_t)stream);
+  return decode_linear(x, ldx, qw, sw, bias, y, ldy, M, N, K, fmt, group, (cudaStream_t)stream);
 }
 
 size_t ql_workspace_bytes(int64_t M, int64_t K) {
@@ -156,7 +179,8 @@ size_t ql_workspace_bytes(int64_t M, int64_t K) {
 }
 
 const char* ql_linear_path(int64_t M, int64_t N, int64_t K, int64_t group) {
-  if (M <= 16) return "gemv_mma";
+  if (M <= 16) return skinny_fused_ok(M, N, K, group) ? "skinny_tcgen05_fused" : "gemv_mma";
+  if (skinny_ok(M, N, K, group)) return "skinny_tcgen05";
   return gemm_kernel_choice(M, N, K, group) == 2 ? "gemm_tcgen05_2cta" : "gemm_tcgen05";
 }
 
@@ -170,14 +194,17 @@ int ql_linear(const void* x, int64_t ldx, const void* qw, const float* sw, const
   if (!aligned(x, 16) || ldx % 8 != 0 || !aligned(qw, 16)) return QL_ERR_MISALIGNED;
   if (int e = check_arch()) return e;
   cudaStream_t st = (cudaStream_t)stream;
-  if (M <= 16)
-    return launch_gemv(x, ldx, nullptr, nullptr, qw, sw, bias, y, ldy, M, N, K, fmt, group, st);
+  if (M <= 16) return decode_linear(x, ldx, qw, sw, bias, y, ldy, M, N, K, fmt, group, st);
   const size_t need = ql_workspace_bytes(M, K);
   if (workspace == nullptr || workspace_bytes < need) return QL_ERR_WORKSPACE;
   if (!aligned(workspace, 16)) return QL_ERR_MISALIGNED;
   uint8_t* qx = static_cast<uint8_t*>(workspace);
   float* sx = reinterpret_cast<float*>(qx + align_up((size_t)M * (size_t)K, 256));
   if (int e = launch_quant_rows(x, M, K, ldx, fmt, qx, sx, st)) return e;
+  if (skinny_ok(M, N, K, group)) {
+    const int r = launch_skinny(qx, sx, qw, sw, bias, y, ldy, nullptr, M, N, K, fmt, group, st);
+    if (r != QL_ERR_BAD_SHAPE) return r;
+  }
   return launch_gemm(qx, sx, qw, sw, bias, y, ldy, nullptr, M, N, K, fmt, group, st);
 }
 

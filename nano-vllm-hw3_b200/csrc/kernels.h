@@ -26,6 +26,18 @@ int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw
                 const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
                 int64_t K, int fmt, int64_t group, cudaStream_t st);
 
+// Cluster split-K weight-streaming tcgen05 kernel for decode-sized M (gemm_skinny.cu).
+int launch_skinny(const void* qx, const float* sx, const void* qw, const float* sw,
+                  const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
+                  int64_t K, int fmt, int64_t group, cudaStream_t st);
+int launch_skinny_fused(const void* x, int64_t ldx, const void* qw, const float* sw,
+                        const void* bias, void* y, int64_t ldy, int64_t M, int64_t N, int64_t K,
+                        int fmt, int64_t group, cudaStream_t st);
+bool skinny_ok(int64_t M, int64_t N, int64_t K, int64_t group);        // pre-quantised path usable
+bool skinny_fused_ok(int64_t M, int64_t N, int64_t K, int64_t group);  // fused path usable (M <= 16)
+void set_skinny_trace(void* buf);  // debug: 16 x int64 device buffer, or nullptr
+bool pdl_enabled();  // QL_PDL=0 disables programmatic dependent launch
+
 // CTA-pair (cta_group::2) tcgen05 GEMM for prefill-sized M, per-row scales only.
 int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* sw,
                  const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,

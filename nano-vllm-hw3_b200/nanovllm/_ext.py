@@ -30,6 +30,7 @@ SIGNATURES = {
     "ql_status_string": (ctypes.c_char_p, [_c_int]),
     "ql_device_check": (_c_int, []),
     "ql_launch_count": (ctypes.c_uint64, []),
+    "ql_debug_set_trace": (None, [_c_vp]),
     "ql_quant_rows": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "ql_quant_groups": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "ql_quant_tensor": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
