@@ -98,7 +98,7 @@ def main():
                                tflops=fl / t / 1e12, gbs=by / t / 1e9, frac=max(t_fl, t_by) / t,
                                bound="tensor" if t_fl >= t_by else "hbm", copies=copies,
                                path=_ext.linear_path(M, N, K, g))
-                    if args.split and M > 16:
+                    if args.split:
                         qs = [_ext.quant_rows(x, dtype) for x in xs]
 
                         def run_q():
@@ -109,11 +109,17 @@ def main():
                             for (q, s), (qx, sx) in zip(ws, qs):
                                 _ext.gemm_w8a8(qx, sx, q, s, None, dtype, g)
 
+                        def run_qg():
+                            for (q, s), x in zip(ws, xs):
+                                qx, sx = _ext.quant_rows(x, dtype)
+                                _ext.gemm_w8a8(qx, sx, q, s, None, dtype, g)
+
+                        rec["chain_us"] = timed_graph(run_qg) / copies * 1e6
                         rec["quant_us"] = timed_graph(run_q) / copies * 1e6
                         rec["gemm_us"] = timed_graph(run_g) / copies * 1e6
                         rec["gemm_tflops"] = fl / (rec["gemm_us"] * 1e-6) / 1e12
                     rows.append(rec)
-                    extra = (f"  quant {rec['quant_us']:.1f}us gemm {rec['gemm_us']:.1f}us "
+                    extra = (f"  q+g chained {rec['chain_us']:.1f}us quant {rec['quant_us']:.1f}us gemm {rec['gemm_us']:.1f}us "
                              f"({rec['gemm_tflops']:.0f} TF)") if "gemm_us" in rec else ""
                     print(f"{model:5s} {name:8s} {mode:8s} {M:5d} {N:6d} {K:6d} {rec['us']:9.2f} "
                           f"{rec['tflops']:9.1f} {rec['gbs']:8.0f} {rec['frac']:6.3f} {rec['bound']:6s} "

@@ -73,7 +73,7 @@ QL_API int ql_device_check(void);
  * gpu_launches and for tests that assert the CUDA path -- not a fallback -- ran). */
 QL_API uint64_t ql_launch_count(void);
 
-/* Debug aid (tools/trace_skinny.py): while a device buffer of 16 int64 is registered, CTA 0 of
+/* Debug aid (tools/trace_skinny.py): while a device buffer of 16 int64 PER CTA is registered, every CTA of
  * the decode kernel stores clock64() stamps of its pipeline phases into it.  NULL switches it
  * off (the default).  Not part of the reference-facing surface. */
 QL_API void ql_debug_set_trace(void* device_buf16_i64);

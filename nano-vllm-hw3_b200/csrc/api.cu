@@ -173,13 +173,18 @@ int ql_gemv_w8a8(const void* x, int64_t ldx, const void* qw, const float* sw, co
 }
 
 size_t ql_workspace_bytes(int64_t M, int64_t K) {
-  if (M <= 16 || K <= 0) return 0;
-  // qx [M,K] (16-byte aligned) followed by sx [M]
+  if (M <= 0 || K <= 0) return 0;
+  // qx [M,K] (16-byte aligned) followed by sx [M].  M <= 16 can run without it (fused quantiser)
+  // but long K slices are faster through the two-launch path, which needs it.
   return align_up((size_t)M * (size_t)K, 256) + align_up((size_t)M * sizeof(float), 256);
 }
 
 const char* ql_linear_path(int64_t M, int64_t N, int64_t K, int64_t group) {
-  if (M <= 16) return skinny_fused_ok(M, N, K, group) ? "skinny_tcgen05_fused" : "gemv_mma";
+  if (M <= 16) {
+    if (skinny_fused_preferred(M, N, K, group)) return "skinny_tcgen05_fused";
+    if (skinny_ok(M, N, K, group)) return "quant+skinny_tcgen05";
+    return skinny_fused_ok(M, N, K, group) ? "skinny_tcgen05_fused" : "gemv_mma";
+  }
   if (skinny_ok(M, N, K, group)) return "skinny_tcgen05";
   return gemm_kernel_choice(M, N, K, group) == 2 ? "gemm_tcgen05_2cta" : "gemm_tcgen05";
 }
@@ -194,8 +199,14 @@ int ql_linear(const void* x, int64_t ldx, const void* qw, const float* sw, const
   if (!aligned(x, 16) || ldx % 8 != 0 || !aligned(qw, 16)) return QL_ERR_MISALIGNED;
   if (int e = check_arch()) return e;
   cudaStream_t st = (cudaStream_t)stream;
-  if (M <= 16) return decode_linear(x, ldx, qw, sw, bias, y, ldy, M, N, K, fmt, group, st);
   const size_t need = ql_workspace_bytes(M, K);
+  if (M <= 16) {
+    // one fused launch while the K slice is short, else quantiser + TMA-fed decode kernel;
+    // without a workspace the fused / GEMV kernels still serve every M <= 16
+    const bool two_launch = !skinny_fused_preferred(M, N, K, group) && skinny_ok(M, N, K, group) &&
+                            workspace != nullptr && workspace_bytes >= need && aligned(workspace, 16);
+    if (!two_launch) return decode_linear(x, ldx, qw, sw, bias, y, ldy, M, N, K, fmt, group, st);
+  }
   if (workspace == nullptr || workspace_bytes < need) return QL_ERR_WORKSPACE;
   if (!aligned(workspace, 16)) return QL_ERR_MISALIGNED;
   uint8_t* qx = static_cast<uint8_t*>(workspace);

@@ -58,9 +58,15 @@ struct SkinnyParams {
   long long* trace;      // debug: clock64() stamps of CTA 0 (ql_debug_set_trace), else nullptr
 };
 
-#define SK_TRACE(i)                                                    \
-  do {                                                                 \
-    if (p.trace != nullptr && blockIdx.x == 0) p.trace[i] = clock64(); \
+// Debug timeline (ql_debug_set_trace): every CTA stamps clock64() into trace[blockIdx.x * 16 + i];
+// slot 15 holds globaltimer at entry so CTAs on different SMs can be aligned.  The buffer must
+// hold 16 int64 per CTA of the largest grid launched while tracing is on.
+#define SK_TRACE(i)                                                              \
+  do {                                                                           \
+    if (p.trace != nullptr) {                                                    \
+      p.trace[(size_t)blockIdx.x * 16 + (i)] = clock64();                        \
+      if ((i) == 0) p.trace[(size_t)blockIdx.x * 16 + 15] = (long long)globaltimer_ns(); \
+    }                                                                            \
   } while (0)
 
 constexpr int kSkThreads = 256;
@@ -118,6 +124,7 @@ skinny_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   float* sx_s = reinterpret_cast<float*>(small + 256);                   // [16]  FUSED
   float* pmax_s = sx_s + 16;                                             // [16]
   float* amax_part = pmax_s + 16;                                        // [8][16]
+  float* inv_s = amax_part + 128;                                        // [16]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) SK_TRACE(0);
@@ -131,15 +138,24 @@ skinny_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   const int kb_begin = u_begin * p.kb_per_g, kb_end = u_end * p.kb_per_g;
   const int nkb = kb_end - kb_begin;
 
+  // Warp 0 owns the ring: it initialises the ring barriers itself and starts streaming weights
+  // (which never depend on the previous kernel) before the rest of the CTA has finished its setup.
+  const int pre = nkb < STAGES ? nkb : STAGES;
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_w);
     if constexpr (!FUSED) tma_prefetch_desc(&tm_x);
-  }
-  if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
     }
+    mbar_fence_init();
+    for (int i = 0; i < pre; ++i) {
+      mbar_expect_tx(&full_bar[i], STAGE);
+      tma_load_2d(ring + i * STAGE, &tm_w, &full_bar[i], (kb_begin + i) * kSkBlockK,
+                  tile_n * kSkTileN, kEvictFirst);
+    }
+  }
+  if (warp == 1 && lane == 0) {
     for (int i = 0; i < NACC; ++i) {
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], 4);
@@ -163,13 +179,6 @@ skinny_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      // Weights are independent of the previous kernel: fill the ring before the PDL wait.
-      const int pre = nkb < STAGES ? nkb : STAGES;
-      for (int i = 0; i < pre; ++i) {
-        mbar_expect_tx(&full_bar[i], STAGE);
-        tma_load_2d(ring + i * STAGE, &tm_w, &full_bar[i], (kb_begin + i) * kSkBlockK,
-                    tile_n * kSkTileN, kEvictFirst);
-      }
       if constexpr (!FUSED) {
         pdl_wait();
         for (int i = 0; i < pre; ++i)
@@ -244,21 +253,44 @@ skinny_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 
     // ===================== fused activation quantiser (M <= 16) =====================
     if constexpr (FUSED) {
+      // Work item = 32 bytes of one activation row (16 bf16 -> one 16-byte chunk of a swizzled
+      // 128-byte B row).  Items are dealt round-robin to the 128 threads, kQU items (2*kQU
+      // 16-byte loads) in flight per thread, so the cost is a few L2 round trips whatever M is.
+      // Every aligned group of 8 lanes works on one row and one K block.
       constexpr float qmax = Fmt<FMT>::qmax;
+      constexpr int kQU = 4;
+      int* pmax_i = reinterpret_cast<int*>(pmax_s);
+      if (e < 16) pmax_i[e] = 0;         // |x| >= 0: float order == int order of the bit patterns
+      asm volatile("bar.sync 1, 128;" ::: "memory");
       pdl_wait();
       if (e == 0) SK_TRACE(3);
-      const int nvec = nkb * 16;       // 16-byte vectors (8 bf16) in this rank's slice of a row
-      const int64_t k0 = (int64_t)kb_begin * kSkBlockK;
-      // pass 1: partial amax of this rank's slice
+      const int nit = nkb * 8;           // items per row in this rank's K slice
+      const int items = p.M * nit;
+      const uint16_t* xk = p.x + (int64_t)kb_begin * kSkBlockK;
+      // pass 1: amax of this rank's slice of every row
 #pragma unroll 1
-      for (int m = q; m < 16; m += 4) {
-        float a = 0.0f;
-        if (m < p.M) {
-          const uint4* xr = reinterpret_cast<const uint4*>(p.x + (int64_t)m * p.ldx + k0);
-          for (int i = lane; i < nvec; i += 32) a = fmaxf(a, amax8(__ldg(xr + i)));
-          a = warp_max(a);
+      for (int base = 0; base < items; base += 128 * kQU) {
+        uint4 v[kQU][2];
+        int mm[kQU];
+#pragma unroll
+        for (int j = 0; j < kQU; ++j) {
+          const int idx = base + j * 128 + e;
+          const bool ok = idx < items;
+          const int m = ok ? idx / nit : 0;
+          const int it = ok ? idx - m * nit : 0;
+          const uint4* src = reinterpret_cast<const uint4*>(xk + (int64_t)m * p.ldx + it * 16);
+          mm[j] = ok ? m : -1;
+          v[j][0] = ok ? __ldg(src) : make_uint4(0, 0, 0, 0);
+          v[j][1] = ok ? __ldg(src + 1) : make_uint4(0, 0, 0, 0);
         }
-        if (lane == 0) pmax_s[m] = a;
+#pragma unroll
+        for (int j = 0; j < kQU; ++j) {
+          float a = fmaxf(amax8(v[j][0]), amax8(v[j][1]));
+          a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, 1));
+          a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, 2));
+          a = fmaxf(a, __shfl_xor_sync(0xffffffffu, a, 4));
+          if ((lane & 7) == 0 && mm[j] >= 0) atomicMax(&pmax_i[mm[j]], __float_as_int(a));
+        }
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (e == 0) SK_TRACE(4);
@@ -274,33 +306,45 @@ skinny_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
         mbar_wait_acq_cluster(amax_bar, 0);
       }
       if (e == 0) SK_TRACE(5);
-      // pass 2: quantise into the UMMA B layout (K-major, 128B swizzle, 8-row groups of 1 KB)
+      if (e < 16) {
+        float amax = pmax_s[e];
+        if (S > 1) {
+          amax = amax_part[e];
+          for (uint32_t s = 1; s < S; ++s) amax = fmaxf(amax, amax_part[s * 16 + e]);
+        }
+        amax = fmaxf(amax, 1e-8f);
+        inv_s[e] = __fdiv_rn(qmax, amax);
+        sx_s[e] = e < p.M ? __fdiv_rn(amax, qmax) : 0.0f;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      // pass 2: quantise into the UMMA B layout (K-major, 128B swizzle, 8-row groups of 1 KB).
+      // Rows >= M of the 16-token operand stay unwritten: a B row only feeds its own
+      // accumulator column, and columns >= M are never read back.
 #pragma unroll 1
-      for (int m = q; m < 16; m += 4) {
-        uint8_t* rowbase = bres + (m >> 3) * 1024 + (m & 7) * 128;
-        const int sw7 = m & 7;
-        if (m < p.M) {
-          float amax = pmax_s[m];
-          if (S > 1) {
-            amax = amax_part[m];
-            for (uint32_t s = 1; s < S; ++s) amax = fmaxf(amax, amax_part[s * 16 + m]);
-          }
-          amax = fmaxf(amax, 1e-8f);
-          const float inv = __fdiv_rn(qmax, amax);
-          if (lane == 0) sx_s[m] = __fdiv_rn(amax, qmax);
-          const uint4* xr = reinterpret_cast<const uint4*>(p.x + (int64_t)m * p.ldx + k0);
-          for (int i = lane; i < nvec; i += 32) {
-            const uint2 qv = quant8_mul<FMT>(__ldg(xr + i), inv);
-            const int kb_l = i >> 4, c = (i >> 1) & 7, half = i & 1;
-            *reinterpret_cast<uint2*>(rowbase + kb_l * (BT * kSkBlockK) + ((c ^ sw7) << 4) + half * 8) = qv;
-          }
-        } else {
-          if (lane == 0) sx_s[m] = 0.0f;
-          for (int i = lane; i < nvec; i += 32) {
-            const int kb_l = i >> 4, c = (i >> 1) & 7, half = i & 1;
-            *reinterpret_cast<uint2*>(rowbase + kb_l * (BT * kSkBlockK) + ((c ^ sw7) << 4) + half * 8) =
-                make_uint2(0, 0);
-          }
+      for (int base = 0; base < items; base += 128 * kQU) {
+        uint4 v[kQU][2];
+        int mm[kQU], ii[kQU];
+#pragma unroll
+        for (int j = 0; j < kQU; ++j) {
+          const int idx = base + j * 128 + e;
+          const bool ok = idx < items;
+          const int m = ok ? idx / nit : 0;
+          const int it = ok ? idx - m * nit : 0;
+          const uint4* src = reinterpret_cast<const uint4*>(xk + (int64_t)m * p.ldx + it * 16);
+          mm[j] = ok ? m : -1;
+          ii[j] = it;
+          v[j][0] = ok ? __ldg(src) : make_uint4(0, 0, 0, 0);
+          v[j][1] = ok ? __ldg(src + 1) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int j = 0; j < kQU; ++j) {
+          if (mm[j] < 0) continue;
+          const int m = mm[j];
+          const float inv = inv_s[m];
+          const uint2 q0 = quant8_mul<FMT>(v[j][0], inv), q1 = quant8_mul<FMT>(v[j][1], inv);
+          uint8_t* dst = bres + (m >> 3) * 1024 + (m & 7) * 128 + (ii[j] >> 3) * (BT * kSkBlockK) +
+                         (((ii[j] & 7) ^ (m & 7)) << 4);
+          *reinterpret_cast<uint4*>(dst) = make_uint4(q0.x, q0.y, q1.x, q1.y);
         }
       }
       fence_proxy_async_smem();
@@ -316,6 +360,19 @@ skinny_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     const int CPB = BT >> lgS;                              // token columns reduced by each rank
     const int lgC = 31 - __clz(CPB);
     const uint32_t recv_local = smem_u32(recv);
+    // final-store coordinates; the weight scales / bias are static, so their loads are issued
+    // here, long before the accumulator is ready, instead of after the reduce barrier
+    const int fg = e & 15, tp = e >> 4;
+    const int nb = tile_n * kSkTileN + fg * 8;
+    const bool vec_ok = !OUT_ACC && (p.ldy % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15) == 0);
+    float swv[8], bv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const bool ok = nb + j < p.N;
+      swv[j] = (!GROUPED && !OUT_ACC && ok) ? __ldg(p.sw + nb + j) : 0.0f;
+      bv[j] = (p.bias != nullptr && ok) ? bf16_lo(p.bias[nb + j]) : 0.0f;
+    }
+    const bool has_bias = p.bias != nullptr;
 
     // column `col` of this rank's partial -> slot [rank][col % CPB][n] of rank col / CPB
     auto scatter = [&](int col, uint32_t v) {
@@ -395,17 +452,6 @@ skinny_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
     if (e == 0) SK_TRACE(12);
     // ---- final: sum the S partials of my CPB token columns, scale, store ----------------------
     if constexpr (!FUSED) pdl_wait();  // sx (and the y buffer) belong to the previous kernels
-    const int fg = e & 15, tp = e >> 4;
-    const int nb = tile_n * kSkTileN + fg * 8;
-    const bool vec_ok = !OUT_ACC && (p.ldy % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15) == 0);
-    float swv[8], bv[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const bool ok = nb + j < p.N;
-      swv[j] = (!GROUPED && !OUT_ACC && ok) ? __ldg(p.sw + nb + j) : 0.0f;
-      bv[j] = (p.bias != nullptr && ok) ? bf16_lo(p.bias[nb + j]) : 0.0f;
-    }
-    const bool has_bias = p.bias != nullptr;
     for (int c = tp; c < CPB; c += 8) {
       const int m = (int)rank * CPB + c;
       if (m >= p.M) break;
@@ -653,11 +699,29 @@ int launch_skinny_fused(const void* x, int64_t ldx, const void* qw, const float*
                    : launch_sk<QL_FP8_E4M3, false, 16, true, false>(nullptr, qw, p, st);
 }
 
+static bool fused_plan(int64_t M, int64_t N, int64_t K, int64_t group, SkPlan& pl, int& nkb_max) {
+  SkinnyParams p = base_params(nullptr, nullptr, nullptr, 0, M, N, K, group);
+  const bool ok = group > 0 ? plan_skinny<true, 16, true>(p, pl) : plan_skinny<false, 16, true>(p, pl);
+  if (ok) nkb_max = ((p.units + pl.S - 1) / pl.S) * p.kb_per_g;
+  return ok;
+}
+
 bool skinny_fused_ok(int64_t M, int64_t N, int64_t K, int64_t group) {
   if (M > 16 || env_int("QL_NO_SKINNY", 0)) return false;
-  SkinnyParams p = base_params(nullptr, nullptr, nullptr, 0, M, N, K, group);
   SkPlan pl;
-  return group > 0 ? plan_skinny<true, 16, true>(p, pl) : plan_skinny<false, 16, true>(p, pl);
+  int nkb_max = 0;
+  return fused_plan(M, N, K, group, pl, nkb_max);
+}
+
+// Measured on B200 (profiles/r1j_fused_vs_two_launch.log): quantiser launch + TMA-fed decode
+// kernel, chained by programmatic dependent launch, beats the fused kernel on every Qwen3 shape
+// (0.6B qkv M=1: 4.9 vs 6.9 us; 8B gate_up M=16: 20.8 vs 44.9 us).  The fused kernel pays two
+// dependent L2 round trips (~1.2 us each while the weight stream saturates the memory system)
+// before its first MMA and its resident 16-row operand squeezes the weight ring.  It therefore
+// only serves callers without a workspace (ql_gemv_w8a8); QL_FUSED=1 forces it for experiments.
+bool skinny_fused_preferred(int64_t M, int64_t N, int64_t K, int64_t group) {
+  if (env_int("QL_FUSED", 0) <= 0) return false;
+  return skinny_fused_ok(M, N, K, group);
 }
 
 bool skinny_ok(int64_t M, int64_t N, int64_t K, int64_t group) {

@@ -20,6 +20,10 @@ __global__ void __launch_bounds__(128)
 quant_rows_kernel(const uint16_t* __restrict__ x, int64_t M, int K, int64_t ldx,
                   uint8_t* __restrict__ q, float* __restrict__ s) {
   __shared__ float red[4];
+  // Programmatic dependent launch: let the consumer (the decode kernel streams its weights while
+  // it waits for qx) start right away; x itself belongs to the previous kernel.
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int ROWS = 4 / WPR;
   const int64_t row = (int64_t)blockIdx.x * ROWS + warp / WPR;
@@ -176,9 +180,19 @@ static int launch_quant_rows_fmt(const void* x, int64_t M, int64_t K, int64_t ld
   const bool vec_ok = (K % 8 == 0) && (ldx % 8 == 0) && ((uintptr_t)x % 16 == 0) &&
                       ((uintptr_t)q % 8 == 0);
   const int K_ = (int)K;
-#define QL_QROWS(NV, WPR)                                                                   \
-  quant_rows_kernel<FMT, NV, WPR><<<(unsigned)((M + (4 / WPR) - 1) / (4 / WPR)), 128, 0, st>>>( \
-      xp, M, K_, ldx, qp, s)
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(128);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+#define QL_QROWS(NV, WPR)                                                     \
+  do {                                                                        \
+    cfg.gridDim = dim3((unsigned)((M + (4 / WPR) - 1) / (4 / WPR)));          \
+    (void)cudaLaunchKernelEx(&cfg, quant_rows_kernel<FMT, NV, WPR>, xp, M, K_, ldx, qp, s); \
+  } while (0)
   if (!vec_ok)
     quant_rows_scalar_kernel<FMT><<<(unsigned)((M + 7) / 8), 256, 0, st>>>(xp, M, K_, ldx, qp, s);
   else if (K <= 1024) QL_QROWS(4, 1);

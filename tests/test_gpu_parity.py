@@ -316,8 +316,9 @@ def _force_split(monkeypatch, S):
 
 
 def test_skinny_dispatch(ext):
-    assert ext.linear_path(1, 4096, 1024) == "skinny_tcgen05_fused"
-    assert ext.linear_path(16, 1024, 3072, 128) == "skinny_tcgen05_fused"
+    assert ext.linear_path(1, 4096, 1024) == "quant+skinny_tcgen05"
+    assert ext.linear_path(16, 1024, 3072, 128) == "quant+skinny_tcgen05"
+    assert ext.linear_path(16, 24576, 4096) == "quant+skinny_tcgen05"   # long K slice: two launches
     assert ext.linear_path(17, 4096, 1024) == "skinny_tcgen05"
     assert ext.linear_path(256, 6144, 4096) == "skinny_tcgen05"
     assert ext.linear_path(128, 6144, 4096, 128) == "skinny_tcgen05"
@@ -346,10 +347,13 @@ def test_skinny_i8_acc_bit_exact(ext, monkeypatch, S, M, N, K):
 @pytest.mark.parametrize("dn", ["i8", "f8"])
 @pytest.mark.parametrize("M,N,K", [(1, 4096, 1024), (2, 1024, 3072), (7, 1000, 1152), (16, 6144, 1024),
                                    (12, 136, 4096), (16, 1024, 8192)])
-def test_skinny_fused_rows(ext, monkeypatch, S, dn, M, N, K):
-    """Fused quantiser (partial amax combined across the cluster, codes written in the UMMA
-    layout by the CTA) + split-K GEMM through ql_linear; strided x and y."""
+@pytest.mark.parametrize("fused", [0, 1])
+def test_skinny_fused_rows(ext, monkeypatch, fused, S, dn, M, N, K):
+    """Decode regime through ql_linear, strided x and y.  fused=1: quantiser inside the kernel
+    (partial amax combined across the cluster, codes written in the UMMA layout by the CTA);
+    fused=0 (the default dispatch): quant_rows launch + TMA-fed split-K kernel."""
     _force_split(monkeypatch, S)
+    monkeypatch.setenv("QL_FUSED", str(fused))
     xb = rand_bf16((M, K + 64), M + N + 5)
     xb[0, 40] = 200.0                              # the row maximum sits in the first K slice only
     if M > 2:
@@ -375,8 +379,10 @@ def test_skinny_fused_rows(ext, monkeypatch, S, dn, M, N, K):
 @pytest.mark.parametrize("dn", ["i8", "f8"])
 @pytest.mark.parametrize("M,N,K,g", [(1, 4096, 1024, 128), (16, 1024, 3072, 128), (5, 520, 1024, 256),
                                      (33, 1024, 1024, 128), (64, 264, 2048, 256), (128, 4096, 1024, 128)])
-def test_skinny_groups(ext, monkeypatch, S, dn, M, N, K, g):
+@pytest.mark.parametrize("fused", [0, 1])
+def test_skinny_groups(ext, monkeypatch, fused, S, dn, M, N, K, g):
     _force_split(monkeypatch, S)
+    monkeypatch.setenv("QL_FUSED", str(fused))
     x, w = rand_bf16((M, K), M + N + 6), rand_bf16((N, K), K + N + 6, 0.02)
     w[1, :g] *= 25.0
     b = rand_bf16((N,), 17)

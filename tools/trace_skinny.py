@@ -1,10 +1,12 @@
 #!/usr/bin/env python
-"""Phase timeline of the decode kernel (gemm_skinny.cu) from its clock64() trace stamps.
+"""Phase timeline of the decode kernel (gemm_skinny.cu) from its per-CTA clock64() trace stamps.
 
-    python tools/trace_skinny.py [--M 1] [--N 4096] [--K 1024] [--group 0] [--dtype int8]
+    python tools/trace_skinny.py [--M 1] [--N 4096] [--K 1024] [--group 0] [--dtype int8] [--prequant]
 
-Registers a 16 x int64 device buffer with ql_debug_set_trace, runs ql_linear a few times and
-prints, for CTA 0, the cycle count of every phase relative to kernel entry (median of runs).
+Registers a [4096 x 16] int64 device buffer with ql_debug_set_trace, runs one ql_linear (or, with
+--prequant, one ql_gemm_w8a8 on pre-quantised activations) after evicting L2 by reading a large
+buffer, and prints for every phase the min / median / max over CTAs of the time since the
+earliest CTA entered the kernel (globaltimer aligns CTAs across SMs, clock64 measures inside).
 """
 import argparse
 import os
@@ -20,6 +22,7 @@ NAMES = ["entry", "setup done", "producer: ring primed", "quant: pdl_wait done",
          "quant: cluster amax", "quant: codes in smem", "mma: B ready", "mma: first stage full",
          "mma: all issued", "epi: accumulator ready", "epi: scattered", "epi: reduce barrier",
          "epi: stored", "exit"]
+MAXG = 4096
 
 
 def main():
@@ -29,34 +32,48 @@ def main():
     ap.add_argument("--K", type=int, default=1024)
     ap.add_argument("--group", type=int, default=0)
     ap.add_argument("--dtype", default="int8")
-    ap.add_argument("--runs", type=int, default=9)
+    ap.add_argument("--prequant", action="store_true")
+    ap.add_argument("--ghz", type=float, default=1.9)
     a = ap.parse_args()
     from nanovllm import _ext
     dt = torch.int8 if a.dtype == "int8" else torch.float8_e4m3fn
     w = (torch.randn(a.N, a.K, device="cuda") * 0.02).to(torch.bfloat16)
     q, s = _ext.quant_groups(w, a.group, dt) if a.group else _ext.quant_rows(w, dt)
     x = torch.randn(a.M, a.K, device="cuda").to(torch.bfloat16)
-    buf = torch.zeros(16, dtype=torch.int64, device="cuda")
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    rows = []
-    _ext.linear(x, q, s, None, dt, a.group)
+    qx, sx = _ext.quant_rows(x, dt)
+    buf = torch.zeros(MAXG * 16, dtype=torch.int64, device="cuda")
+    flush = torch.ones(512 << 20, dtype=torch.uint8, device="cuda")
+
+    def run():
+        if a.prequant:
+            return _ext.gemm_w8a8(qx, sx, q, s, None, dt, a.group)
+        return _ext.linear(x, q, s, None, dt, a.group)
+
+    run()
     _ext.load().ql_debug_set_trace(buf.data_ptr())
-    for _ in range(a.runs):
-        flush.zero_()                      # weights come from HBM, as in a real decode step
+    for _ in range(3):
+        flush.sum()                        # evict by READING: no dirty lines compete with the kernel
         buf.zero_()
+        x.add_(0)                          # bring the activations back into L2, as in a real decode step
+        qx.add_(0)
         torch.cuda.synchronize()
-        _ext.linear(x, q, s, None, dt, a.group)
+        run()
         torch.cuda.synchronize()
-        rows.append(buf.cpu().tolist())
     _ext.load().ql_debug_set_trace(None)
-    print(f"M={a.M} N={a.N} K={a.K} g={a.group} {a.dtype} path={_ext.linear_path(a.M, a.N, a.K, a.group)}")
-    med = []
-    for i in range(15):
-        v = sorted(r[i] - r[0] for r in rows if r[i] != 0)
-        med.append(v[len(v) // 2] if v else None)
+    t = buf.cpu().view(MAXG, 16)
+    live = t[:, 0] != 0
+    t = t[live]
+    g0 = t[:, 15].min()
+    print(f"M={a.M} N={a.N} K={a.K} g={a.group} {a.dtype} prequant={a.prequant} "
+          f"path={_ext.linear_path(a.M, a.N, a.K, a.group)} CTAs={t.shape[0]}")
+    entry_ns = (t[:, 15] - g0).double()
+    print(f"  {'phase':30s} {'min':>8s} {'median':>8s} {'max':>8s}   (ns since the first CTA's entry)")
     for i, name in enumerate(NAMES):
-        if med[i] is not None:
-            print(f"  {i:2d} {name:28s} {med[i]:8d} cyc  ({med[i] / 1.9:8.0f} ns @1.9GHz)")
+        ok = t[:, i] != 0
+        if not ok.any():
+            continue
+        v = entry_ns[ok] + (t[ok, i] - t[ok, 0]).double() / a.ghz
+        print(f"  {i:2d} {name:27s} {v.min().item():8.0f} {v.median().item():8.0f} {v.max().item():8.0f}")
 
 
 if __name__ == "__main__":
