@@ -54,6 +54,17 @@ def load_peaks():
     return dict(hbm=6650.0, bf16=1590.0, bf16_sus=1400.0, src="fallback (B200_PROFILING.md)")
 
 
+def load_traffic(key):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of
+    this same command (profiles/traffic.json, written by tools/ncu_traffic.py); None when the
+    capture was taken on another workload."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None
+    d = json.load(open(p))
+    return d.get("traffic_bytes_per_launch") if d.get("workload", key) == key else None
+
+
 def layer_shapes(m, tp=1):
     """[(name, N, K)] per rank for one decoder layer."""
     qkv_n = (m["heads"] + 2 * m["kv"]) * m["hd"]
@@ -346,6 +357,7 @@ def main():
     from nanovllm import _ext
     assert _ext.load().ql_device_check() == 0
     peaks = load_peaks()
+    workload_key = f"{args.model}/{args.dtype}/{args.quant}/{group}/T{T_rank}/tp{world}"
 
     stack = LinearStack(m, dtype, args.quant, group, "cuda", seed=0)
     T = T_rank * world                                     # every TP rank sees every token
@@ -446,7 +458,7 @@ def main():
     else:
         roof = {"bound": "hbm", "achieved": k_by / t_k / 1e9, "peak": peaks["hbm"], "unit": "GB/s"}
     roof["frac"] = roof["achieved"] / roof["peak"]
-    roof.update(traffic=None,
+    roof.update(traffic=load_traffic(workload_key),
                 kernel=("gemv_kernel" if T <= 16 else
                         "gemm2_kernel (tcgen05 cta_group::2)" if _ext.linear_path(T, shapes[0][1], shapes[0][2], group)
                         .endswith("2cta") else "gemm_kernel (tcgen05)"),
