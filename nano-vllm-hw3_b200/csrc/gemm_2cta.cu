@@ -205,6 +205,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();   // the next kernel (a quantiser) may become resident and wait
 
   const int num_kb = p.K / kG2BlockK;
   const int total_tiles = p.tiles_m * p.tiles_n;
@@ -213,24 +214,45 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
     if (lane == 0) {
-      int stage = 0;
+      // Programmatic dependent launch: the weights never depend on the previous kernel, so the
+      // first ring fill's B halves are requested before griddepcontrol.wait (the quantiser that
+      // writes qx / sx may still be running); A loads and everything after sit behind the wait.
+      int pre = 0;
+      {
+        int stage = 0;
+        for (int tile = pair; tile < total_tiles && pre < kG2Stages; tile += num_pairs) {
+          int tm, tn;
+          tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+          const int row_b = tn * kG2TileN + (int)cta * kG2RowsB;
+          for (int kb = 0; kb < num_kb && pre < kG2Stages; ++kb, ++pre, ++stage) {
+            const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[stage]), 0);
+            if (cta == 0) mbar_expect_tx(&full_bar[stage], 2 * kG2Stage);
+            tma_load_2d_pair(smem_gen + stage * kG2Stage + kG2StageA, &tm_w, full_leader,
+                             kb * kG2BlockK, row_b);
+          }
+        }
+      }
+      pdl_wait();
+      int stage = 0, it = 0;
       uint32_t phase = 0;
       for (int tile = pair; tile < total_tiles; tile += num_pairs) {
         int tm, tn;
         tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
         const int row_a = tm * 2 * kG2RowsA + (int)cta * kG2RowsA;
         const int row_b = tn * kG2TileN + (int)cta * kG2RowsB;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          // Both CTAs' bytes are counted on the leader's barrier; only the leader arrives
-          // (a local, fence-free operation).  The peer's bytes may land before the leader's
-          // expect_tx of the same phase: the transaction count goes negative transiently and
-          // the phase still cannot complete before the leader's arrival.
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[stage]), 0);
-          if (cta == 0) mbar_expect_tx(&full_bar[stage], 2 * kG2Stage);
           uint8_t* sa = smem_gen + stage * kG2Stage;
+          if (it >= pre) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            // Both CTAs' bytes are counted on the leader's barrier; only the leader arrives
+            // (a local, fence-free operation).  The peer's bytes may land before the leader's
+            // expect_tx of the same phase: the transaction count goes negative transiently and
+            // the phase still cannot complete before the leader's arrival.
+            if (cta == 0) mbar_expect_tx(&full_bar[stage], 2 * kG2Stage);
+            tma_load_2d_pair(sa + kG2StageA, &tm_w, full_leader, kb * kG2BlockK, row_b);
+          }
           tma_load_2d_pair(sa, &tm_x, full_leader, kb * kG2BlockK, row_a);
-          tma_load_2d_pair(sa + kG2StageA, &tm_w, full_leader, kb * kG2BlockK, row_b);
           if (++stage == kG2Stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -282,6 +304,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
     const uint32_t out = stage_out + lane * 128;
     int acc = 0;
     uint32_t acc_phase = 0;
+    pdl_wait();   // sx and the y buffer belong to the previous kernels
 
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       int tm, tn;
@@ -435,9 +458,23 @@ static int launch_g2(const void* qx, const void* qw, void* y, int64_t ldy, Gemm2
       fprintf(stderr, "[qlinear_b200] gemm2: %d co-resident CTA pairs on %d SMs\n", n, num_sms());
   }
   const int pairs = (int)(tiles < pairs_max ? tiles : pairs_max);
-  kern<<<2 * pairs, kG2Threads, kG2Smem, st>>>(tm_x, tm_w, tm_y, p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * pairs));
+  cfg.blockDim = dim3(kG2Threads);
+  cfg.dynamicSmemBytes = kG2Smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  const cudaError_t err = cudaLaunchKernelEx(&cfg, kern, tm_x, tm_w, tm_y, p);
   count_launch();
-  return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
+  if (err != cudaSuccess) {
+    (void)cudaGetLastError();
+    return QL_ERR_CUDA;
+  }
+  return QL_OK;
 }
 
 bool gemm2_eligible(const void* y, int64_t ldy, const void* sw, const void* bias, bool out_acc) {
