@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define QL_ABI_VERSION 2
+#define QL_ABI_VERSION 3
 
 /* status codes */
 #define QL_OK 0
@@ -150,6 +150,37 @@ QL_API int ql_gemv_w8a8(const void* x, int64_t ldx, const void* qw, const float*
 QL_API int ql_linear(const void* x, int64_t ldx, const void* qw, const float* sw, const void* bias,
               void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int fmt, int64_t group,
               void* workspace, size_t workspace_bytes, ql_stream_t stream);
+
+/*
+ * RMSNorm (optionally with the residual add) fused with the per-token quantiser: the producer of
+ * qkv_proj's and gate_up_proj's input.
+ * Replaces RMSNorm.rms_forward / add_rms_forward, nanovllm/layers/layernorm.py:16-40 (called at
+ * nanovllm/models/qwen3.py:156-165) followed by per_row_quant (quantization.py:147-163) inside
+ * per_row_matmul (:325):
+ *   xf = float(x) [+ float(residual_in)];  residual_out = bf16(xf)
+ *   h  = bf16( float(bf16(xf * rsqrt(mean(xf^2) + eps))) * float(weight) )
+ *   (q, s) = ql_quant_rows(h)
+ * x bf16 [M, K] with row stride ldx; residual_in / residual_out bf16 [M, K] dense, both NULL or
+ * both set (they may alias: the engine updates the residual stream in place); weight bf16 [K];
+ * q [M, K] codes + s [M] (q == NULL: no quantised output); h_out bf16 [M, K] dense or NULL (the
+ * bf16 result is only materialised on request).  K % 8 == 0, K <= 51200.  The pair (q, s) feeds
+ * ql_gemm_w8a8 directly.
+ */
+QL_API int ql_rmsnorm_quant(const void* x, int64_t ldx, const void* residual_in, void* residual_out,
+                     const void* weight, float eps, int64_t M, int64_t K, int fmt, void* q,
+                     float* s, void* h_out, ql_stream_t stream);
+
+/*
+ * SiLU(gate) * up fused with the per-token quantiser: the producer of down_proj's input.
+ * Replaces SiluAndMul.forward, nanovllm/layers/activation.py:11-14 (called at
+ * nanovllm/models/qwen3.py:117) followed by per_row_quant inside per_row_matmul:
+ *   h = bf16( float(bf16(silu(float(gate)))) * float(up) );  (q, s) = ql_quant_rows(h)
+ * gate_up bf16 [M, 2*I] with row stride ld (gate = columns [0, I), up = [I, 2I), the layout
+ * MergedColumnParallelLinear produces, linear.py:76-93); q [M, I], s [M], h_out bf16 [M, I] dense
+ * or NULL; q == NULL: bf16 output only.  I % 8 == 0, I <= 102400.
+ */
+QL_API int ql_silu_mul_quant(const void* gate_up, int64_t ld, int64_t M, int64_t I, int fmt, void* q,
+                      float* s, void* h_out, ql_stream_t stream);
 
 /* Bytes of caller-provided scratch ql_linear needs for an [M, K] activation (0 for M <= 16). */
 QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);

@@ -172,6 +172,38 @@ int ql_gemv_w8a8(const void* x, int64_t ldx, const void* qw, const float* sw, co
   return decode_linear(x, ldx, qw, sw, bias, y, ldy, M, N, K, fmt, group, (cudaStream_t)stream);
 }
 
+int ql_rmsnorm_quant(const void* x, int64_t ldx, const void* residual_in, void* residual_out,
+                      const void* weight, float eps, int64_t M, int64_t K, int fmt, void* q,
+                      float* s, void* h_out, ql_stream_t stream) {
+  if (q != nullptr && !fmt_ok(fmt)) return QL_ERR_BAD_FORMAT;
+  if (M < 0 || K <= 0 || K % 8 != 0 || ldx < K) return QL_ERR_BAD_SHAPE;
+  if (M == 0) return QL_OK;
+  if (!x || !weight || (q == nullptr && h_out == nullptr) || (q != nullptr && s == nullptr))
+    return QL_ERR_NULL;
+  if ((residual_in == nullptr) != (residual_out == nullptr)) return QL_ERR_NULL;
+  if (!aligned(x, 16) || ldx % 8 != 0 || !aligned(weight, 16) || !aligned(residual_in, 16) ||
+      !aligned(residual_out, 16) || !aligned(q, 8) || !aligned(h_out, 16))
+    return QL_ERR_MISALIGNED;
+  if ((size_t)K * 4 > 200 * 1024) return QL_ERR_BAD_SHAPE;   // the row lives in shared memory
+  if (int e = check_arch()) return e;
+  return launch_rmsnorm_quant(x, ldx, residual_in, residual_out, weight, eps, M, K, fmt, q, s,
+                              h_out, (cudaStream_t)stream);
+}
+
+int ql_silu_mul_quant(const void* gate_up, int64_t ld, int64_t M, int64_t I, int fmt, void* q,
+                      float* s, void* h_out, ql_stream_t stream) {
+  if (q != nullptr && !fmt_ok(fmt)) return QL_ERR_BAD_FORMAT;
+  if (M < 0 || I <= 0 || I % 8 != 0 || ld < 2 * I) return QL_ERR_BAD_SHAPE;
+  if (M == 0) return QL_OK;
+  if (!gate_up || (q == nullptr && h_out == nullptr) || (q != nullptr && s == nullptr))
+    return QL_ERR_NULL;
+  if (!aligned(gate_up, 16) || ld % 8 != 0 || !aligned(q, 8) || !aligned(h_out, 16))
+    return QL_ERR_MISALIGNED;
+  if ((size_t)I * 2 > 200 * 1024) return QL_ERR_BAD_SHAPE;   // the row lives in shared memory
+  if (int e = check_arch()) return e;
+  return launch_silu_mul_quant(gate_up, ld, M, I, fmt, q, s, h_out, (cudaStream_t)stream);
+}
+
 size_t ql_workspace_bytes(int64_t M, int64_t K) {
   if (M <= 0 || K <= 0) return 0;
   // qx [M,K] (16-byte aligned) followed by sx [M].  M <= 16 can run without it (fused quantiser)

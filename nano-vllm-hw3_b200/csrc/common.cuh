@@ -27,14 +27,23 @@ __device__ __forceinline__ uint16_t f2bf(float f) {
   return __bfloat16_as_ushort(__float2bfloat16_rn(f));
 }
 
+// roundf(v) (half away from zero) as an integer, for |v| < 2^22, without the quarter-rate F2I /
+// FRND conversions: n = floor(|v| + 0.5) where both additions round toward zero -- RZ never
+// carries a sum across an integer, so floor(RZ(|v| + 0.5)) == floor(|v| + 0.5) exactly, and
+// RZ(t + 2^23) leaves floor(t) in the low mantissa bits.
+__device__ __forceinline__ int round_away_i8(float v) {
+  const float t = __fadd_rz(fabsf(v), 0.5f);
+  const int n = __float_as_int(__fadd_rz(t, 8388608.0f)) & 0x7fffff;
+  return v < 0.0f ? -n : n;
+}
+
 // Quantise two scaled values to one 16-bit pair of codes.
 //   int8: round half away from zero (libdevice.round, reference quantization.py:41)
 //   fp8 : cvt.rn.satfinite.e4m3x2.f32 (reference :39)
 template <int FMT>
 __device__ __forceinline__ uint32_t quant_pair_away(float a, float b) {
   if constexpr (FMT == QL_INT8) {
-    int ia = (int)roundf(a), ib = (int)roundf(b);
-    return (uint32_t)(ia & 0xff) | ((uint32_t)(ib & 0xff) << 8);
+    return (uint32_t)(round_away_i8(a) & 0xff) | ((uint32_t)(round_away_i8(b) & 0xff) << 8);
   } else {
     return (uint32_t)__nv_cvt_float2_to_fp8x2(make_float2(a, b), __NV_SATFINITE, __NV_E4M3);
   }

@@ -115,6 +115,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
 
   const int num_kb = p.K / kBlockK;
   const int total_tiles = p.tiles_n * p.tiles_m;
@@ -122,16 +123,34 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      int stage = 0;
+      // programmatic dependent launch: weight tiles of the first ring fill are requested before
+      // griddepcontrol.wait; the activation loads (written by the quantiser) come after it
+      int pre = 0;
+      {
+        int stage = 0;
+        for (int tile = blockIdx.x; tile < total_tiles && pre < STAGES; tile += gridDim.x) {
+          int tm, tn;
+          tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+          for (int kb = 0; kb < num_kb && pre < STAGES; ++kb, ++pre, ++stage) {
+            mbar_expect_tx(&full_bar[stage], Cfg::stage);
+            tma_load_2d(smem + stage * Cfg::stage, &tm_w, &full_bar[stage], kb * kBlockK,
+                        tn * kTileN, kEvictNormal);
+          }
+        }
+      }
+      pdl_wait();
+      int stage = 0, it = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         int tm, tn;
         tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
           uint8_t* sa = smem + stage * Cfg::stage;
-          mbar_expect_tx(&full_bar[stage], Cfg::stage);
-          tma_load_2d(sa, &tm_w, &full_bar[stage], kb * kBlockK, tn * kTileN, kEvictNormal);
+          if (it >= pre) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_expect_tx(&full_bar[stage], Cfg::stage);
+            tma_load_2d(sa, &tm_w, &full_bar[stage], kb * kBlockK, tn * kTileN, kEvictNormal);
+          }
           tma_load_2d(sa + Cfg::stage_a, &tm_x, &full_bar[stage], kb * kBlockK, tm * BT,
                       kEvictNormal);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -191,6 +210,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
     const bool vec_ok = (p.ldy % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15) == 0);
     int acc = 0;
     uint32_t acc_phase = 0;
+    pdl_wait();   // sx and the y buffer belong to the previous kernels
 
     // v[i] = value of (token mc + i, this thread's feature n), already scaled; -> bf16 -> y
     auto store_chunk = [&](const float (&v)[32], int mc, int nq0) {
@@ -397,9 +417,23 @@ static int launch_cfg(const void* qx, const void* qw, GemmParams p, cudaStream_t
   }
   const int64_t tiles = (int64_t)p.tiles_n * p.tiles_m;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
-  kern<<<grid, kGemmThreads, Cfg::smem_bytes, st>>>(tm_w, tm_x, p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = Cfg::smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  const cudaError_t err = cudaLaunchKernelEx(&cfg, kern, tm_w, tm_x, p);
   count_launch();
-  return cudaGetLastError() == cudaSuccess ? QL_OK : QL_ERR_CUDA;
+  if (err != cudaSuccess) {
+    (void)cudaGetLastError();
+    return QL_ERR_CUDA;
+  }
+  return QL_OK;
 }
 
 // Token-tile width: smallest tile covering M for M <= 128; above that the width with the

@@ -39,6 +39,13 @@ bool skinny_fused_preferred(int64_t M, int64_t N, int64_t K, int64_t group);  //
 void set_skinny_trace(void* buf);  // debug: 16 x int64 device buffer, or nullptr
 bool pdl_enabled();  // QL_PDL=0 disables programmatic dependent launch
 
+// Producers fused with the per-token quantiser (producers.cu).  q == nullptr: bf16 output only.
+int launch_rmsnorm_quant(const void* x, int64_t ldx, const void* res_in, void* res_out,
+                         const void* w, float eps, int64_t M, int64_t K, int fmt, void* q,
+                         float* s, void* h_out, cudaStream_t st);
+int launch_silu_mul_quant(const void* gate_up, int64_t ld, int64_t M, int64_t I, int fmt, void* q,
+                          float* s, void* h_out, cudaStream_t st);
+
 // CTA-pair (cta_group::2) tcgen05 GEMM for prefill-sized M, per-row scales only.
 int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* sw,
                  const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,

@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libqlinear_b200.so")
 
 QL_INT8, QL_FP8_E4M3 = 0, 1
-QL_ABI_VERSION = 2
+QL_ABI_VERSION = 3
 _FMT = {torch.int8: QL_INT8, torch.float8_e4m3fn: QL_FP8_E4M3}
 
 _c_i64, _c_int, _c_vp, _c_sz = ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
@@ -41,6 +41,9 @@ SIGNATURES = {
                               _c_i64, _c_int, _c_i64, _c_vp]),
     "ql_linear": (_c_int, [_c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64,
                            _c_i64, _c_int, _c_i64, _c_vp, _c_sz, _c_vp]),
+    "ql_rmsnorm_quant": (_c_int, [_c_vp, _c_i64, _c_vp, _c_vp, _c_vp, ctypes.c_float, _c_i64, _c_i64,
+                                  _c_int, _c_vp, _c_vp, _c_vp, _c_vp]),
+    "ql_silu_mul_quant": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp, _c_vp]),
     "ql_workspace_bytes": (_c_sz, [_c_i64, _c_i64]),
     "ql_linear_path": (ctypes.c_char_p, [_c_i64, _c_i64, _c_i64, _c_i64]),
 }
@@ -222,6 +225,44 @@ def gemv_w8a8(x, qw, sw, bias, dtype, group_size: int = 0):
         _check(load().ql_gemv_w8a8(_ptr(x2), x2.stride(0) if M > 1 else K, _ptr(qw), _ptr(sw),
                                    _ptr(bias), _ptr(y), N, M, N, K, fmt, group_size, _stream(x)))
     return y.view(y_shape)
+
+
+@torch.no_grad()
+def rmsnorm_quant(x, weight, eps: float, residual=None, dtype=None, want_bf16: bool = False):
+    """ql_rmsnorm_quant.  x bf16 [M,K]; residual bf16 [M,K] or None (updated IN PLACE to x + residual,
+    as the engine's residual stream).  Returns (q, s, h): q/s None when dtype is None, h None
+    unless want_bf16 (or dtype is None)."""
+    assert x.dtype == torch.bfloat16 and x.dim() == 2 and weight.dtype == torch.bfloat16
+    _cuda_rowmajor(x, "x")
+    M, K = x.shape
+    assert weight.numel() == K and weight.is_contiguous()
+    if residual is not None:
+        assert residual.shape == x.shape and residual.dtype == torch.bfloat16 and residual.is_contiguous()
+    fmt = fmt_of(dtype) if dtype is not None else 0
+    q = torch.empty((M, K), dtype=dtype, device=x.device) if dtype is not None else None
+    s = torch.empty((M,), dtype=torch.float32, device=x.device) if dtype is not None else None
+    h = torch.empty((M, K), dtype=torch.bfloat16, device=x.device) if (want_bf16 or dtype is None) else None
+    with torch.cuda.device(x.device):
+        _check(load().ql_rmsnorm_quant(_ptr(x), x.stride(0) if M > 1 else K, _ptr(residual), _ptr(residual),
+                                       _ptr(weight), float(eps), M, K, fmt, _ptr(q), _ptr(s), _ptr(h),
+                                       _stream(x)))
+    return q, s, h
+
+
+@torch.no_grad()
+def silu_mul_quant(gate_up, dtype=None, want_bf16: bool = False):
+    """ql_silu_mul_quant.  gate_up bf16 [M, 2I] -> (q [M,I], s [M], h bf16 [M,I] or None)."""
+    assert gate_up.dtype == torch.bfloat16 and gate_up.dim() == 2 and gate_up.shape[1] % 2 == 0
+    _cuda_rowmajor(gate_up, "gate_up")
+    M, I = gate_up.shape[0], gate_up.shape[1] // 2
+    fmt = fmt_of(dtype) if dtype is not None else 0
+    q = torch.empty((M, I), dtype=dtype, device=gate_up.device) if dtype is not None else None
+    s = torch.empty((M,), dtype=torch.float32, device=gate_up.device) if dtype is not None else None
+    h = torch.empty((M, I), dtype=torch.bfloat16, device=gate_up.device) if (want_bf16 or dtype is None) else None
+    with torch.cuda.device(gate_up.device):
+        _check(load().ql_silu_mul_quant(_ptr(gate_up), gate_up.stride(0) if M > 1 else 2 * I, M, I, fmt,
+                                        _ptr(q), _ptr(s), _ptr(h), _stream(gate_up)))
+    return q, s, h
 
 
 def launch_count() -> int:

@@ -94,10 +94,15 @@ class LinearBase(nn.Module):
     def is_quantized(self) -> bool:
         return self.qw is not None
 
-    def _linear(self, x: torch.Tensor, bias: torch.Tensor | None) -> torch.Tensor:
+    def _linear(self, x, bias: torch.Tensor | None) -> torch.Tensor:
         if self.qw is None:
             return F.linear(x, self.weight, bias)
         b = None if bias is None else bias.data
+        if hasattr(x, "q") and hasattr(x, "s"):
+            # QuantizedActivation from a fused producer (layers/layernorm.py, layers/activation.py):
+            # this linear's per_row_quant launch is skipped
+            assert x.q.dtype == self.qdtype, "producer and linear must use the same 8-bit format"
+            return _ext.gemm_w8a8(x.q, x.s, self.qw, self._sw_kernel, b, self.qdtype, self.group_size)
         return _ext.linear(x, self.qw, self._sw_kernel, b, self.qdtype, self.group_size)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
