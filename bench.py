@@ -421,16 +421,15 @@ def main():
     for (_, N, K) in shapes:
         if K not in acts:
             xa = torch.randn(T, K, device="cuda", dtype=torch.float32, generator=gx).to(torch.bfloat16)
-            acts[K] = (xa,) + tuple(_ext.quant_rows(xa, dtype)) if T > 16 else (xa,)
+            acts[K] = (xa,) + tuple(_ext.quant_rows(xa, dtype))
 
     def kernels_only():
+        # the GEMM / decode kernel of every linear on pre-quantised activations (the kernel
+        # ql_linear launches after its quantiser, for every T)
         for mods in stack.layers:
             for mod in mods:
                 K = mod.qw.shape[1]
-                if T > 16:
-                    _ext.gemm_w8a8(acts[K][1], acts[K][2], mod.qw, mod._sw_kernel, None, dtype, mod.group_size)
-                else:
-                    _ext.gemv_w8a8(acts[K][0], mod.qw, mod._sw_kernel, None, dtype, mod.group_size)
+                _ext.gemm_w8a8(acts[K][1], acts[K][2], mod.qw, mod._sw_kernel, None, dtype, mod.group_size)
 
     if use_graph:
         ks = torch.cuda.Stream()
@@ -444,12 +443,9 @@ def main():
         ms_k = time_steps(kgr.replay, max(args.steps // 2, 2), 3, False)
     else:
         ms_k = time_steps(kernels_only, max(args.steps // 2, 2), 3, False)
-    if T > 16:
-        k_fl = sum(2 * T * N * K for _, N, K in shapes) * m["layers"]
-        k_by = sum(T * K + N * K + 4 * T + 4 * N * (K // group if group else 1) + 2 * T * N
-                   for _, N, K in shapes) * m["layers"]
-    else:
-        k_fl, k_by = fl_layer * m["layers"], by_layer * m["layers"]
+    k_fl = sum(2 * T * N * K for _, N, K in shapes) * m["layers"]
+    k_by = sum(T * K + N * K + 4 * T + 4 * N * (K // group if group else 1) + 2 * T * N
+               for _, N, K in shapes) * m["layers"]
     t_k = ms_k * 1e-3
     tensor_peak = 2.0 * peaks["bf16"]                     # 8-bit dense rate = 2 x bf16 on sm_100
     t_fl, t_by = k_fl / (tensor_peak * 1e12), k_by / (peaks["hbm"] * 1e9)
@@ -459,9 +455,10 @@ def main():
         roof = {"bound": "hbm", "achieved": k_by / t_k / 1e9, "peak": peaks["hbm"], "unit": "GB/s"}
     roof["frac"] = roof["achieved"] / roof["peak"]
     roof.update(traffic=load_traffic(workload_key),
-                kernel=("gemv_kernel" if T <= 16 else
-                        "gemm2_kernel (tcgen05 cta_group::2)" if _ext.linear_path(T, shapes[0][1], shapes[0][2], group)
-                        .endswith("2cta") else "gemm_kernel (tcgen05)"),
+                kernel={"gemm_tcgen05_2cta": "gemm2_kernel (tcgen05 cta_group::2)",
+                        "gemm_tcgen05": "gemm_kernel (tcgen05)"}.get(
+                            _ext.linear_path(T, shapes[0][1], shapes[0][2], group).replace("quant+", ""),
+                            "skinny_kernel (tcgen05 cluster split-K)"),
                 launches=n_lin, avg_launch_us=ms_k * 1e3 / n_lin,
                 tflops=k_fl / t_k / 1e12, gbs=k_by / t_k / 1e9,
                 share_of_step=ms_k / ms,

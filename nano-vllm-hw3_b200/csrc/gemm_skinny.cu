@@ -724,9 +724,16 @@ bool skinny_fused_preferred(int64_t M, int64_t N, int64_t K, int64_t group) {
   return skinny_fused_ok(M, N, K, group);
 }
 
+// Where the split-K decode kernel beats the tiled GEMMs, measured on B200 over the Qwen3 shapes
+// (profiles/r1n_dispatch_crossover.log; whole ql_linear, graph replay): always up to 32 tokens;
+// beyond that only while the K split buys parallelism the N x M tiling cannot -- long K relative
+// to N -- because above 64 tokens a 256-wide CTA-pair tile already amortises the weight stream.
 bool skinny_ok(int64_t M, int64_t N, int64_t K, int64_t group) {
-  (void)N; (void)K;
-  return M <= skinny_max_m(group) && !env_int("QL_NO_SKINNY", 0);
+  if (M > skinny_max_m(group) || env_int("QL_NO_SKINNY", 0)) return false;
+  if (group > 0 || M <= 32 || env_int("QL_SKINNY_ALWAYS", 0)) return true;
+  if (M <= 64) return K >= 2048;
+  if (M <= 128) return K >= 2 * N;
+  return K >= 2 * N && K >= 8192;
 }
 
 }  // namespace ql

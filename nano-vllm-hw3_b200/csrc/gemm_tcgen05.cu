@@ -461,8 +461,8 @@ static int launch_bt(const void* qx, const void* qw, const GemmParams& p, cudaSt
   }
 }
 
-// Kernel choice.  The CTA-pair kernel needs enough 256x256 tiles to occupy the 74 SM pairs;
-// below that the single-CTA kernel's 128 x {32..256} tiles spread the work over more SMs.
+// Kernel choice between the CTA-pair kernel (256x256 tiles) and the single-CTA kernel
+// (128 x {32..256} tiles, the only one with per-group scales).
 // QL_FORCE_GEMM=1|2 (read once) pins the choice for sweeps and tests.
 int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group) {
   (void)K;
@@ -473,8 +473,10 @@ int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group) {
     forced = (e != nullptr && (e[0] == '1' || e[0] == '2')) ? e[0] - '0' : 0;
   }
   if (forced) return forced;
-  const int64_t tiles2 = ((M + 255) / 256) * ((N + 255) / 256);
-  return (M >= 512 && tiles2 >= 32) ? 2 : 1;
+  // measured (profiles/r1n_dispatch_crossover.log): from 128 tokens on the pair kernel wins on
+  // every Qwen3 shape, even with as few as 4 tiles (its TMA-store epilogue is much shorter)
+  (void)N;
+  return M >= 128 ? 2 : 1;
 }
 
 int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw,

@@ -309,6 +309,7 @@ def test_gemv_groups(ext, dn, M, N, K, g):
 # ------------------------------------------------------------------ decode regime: cluster split-K tcgen05 kernel
 
 def _force_split(monkeypatch, S):
+    monkeypatch.setenv("QL_SKINNY_ALWAYS", "1")     # these tests target the decode kernel at every M <= 256
     if S:
         monkeypatch.setenv("QL_SKINNY_S", str(S))
     else:
@@ -316,14 +317,20 @@ def _force_split(monkeypatch, S):
 
 
 def test_skinny_dispatch(ext):
+    """Dispatch measured in profiles/r1n_dispatch_crossover.log."""
     assert ext.linear_path(1, 4096, 1024) == "quant+skinny_tcgen05"
     assert ext.linear_path(16, 1024, 3072, 128) == "quant+skinny_tcgen05"
     assert ext.linear_path(16, 24576, 4096) == "quant+skinny_tcgen05"   # long K slice: two launches
     assert ext.linear_path(17, 4096, 1024) == "skinny_tcgen05"
-    assert ext.linear_path(256, 6144, 4096) == "skinny_tcgen05"
+    assert ext.linear_path(64, 4096, 1024) == "gemm_tcgen05"            # short K: no split-K gain
+    assert ext.linear_path(64, 6144, 4096) == "skinny_tcgen05"
+    assert ext.linear_path(128, 1024, 3072) == "skinny_tcgen05"         # K >= 2N
+    assert ext.linear_path(128, 6144, 4096) == "gemm_tcgen05_2cta"
+    assert ext.linear_path(256, 4096, 12288) == "skinny_tcgen05"
+    assert ext.linear_path(256, 6144, 4096) == "gemm_tcgen05_2cta"
     assert ext.linear_path(128, 6144, 4096, 128) == "skinny_tcgen05"
     assert ext.linear_path(129, 6144, 4096, 128) == "gemm_tcgen05"
-    assert ext.linear_path(257, 6144, 4096) == "gemm_tcgen05"
+    assert ext.linear_path(257, 4096, 12288) == "gemm_tcgen05_2cta"
 
 
 @pytest.mark.parametrize("S", [0, 1, 2, 4, 8])
