@@ -489,9 +489,16 @@ def main():
                                 "sample": f"2 of {m['layers']} layers x {T_s} tokens, median of 3 passes after "
                                           f"1 warm-up, scaled to {m['layers']} layers"}
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if dist_on:
-        dist.destroy_process_group()
+        # The captured graphs hold NCCL kernels; tearing the communicator down under them hung
+        # the first TP=2 run after the line was printed (profiles/r1o_*).  Everything is measured
+        # and flushed: meet once more, then leave without the NCCL destructor.
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
