@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define QL_ABI_VERSION 3
+#define QL_ABI_VERSION 4
 
 /* status codes */
 #define QL_OK 0
@@ -181,6 +181,28 @@ QL_API int ql_rmsnorm_quant(const void* x, int64_t ldx, const void* residual_in,
  */
 QL_API int ql_silu_mul_quant(const void* gate_up, int64_t ld, int64_t M, int64_t I, int fmt, void* q,
                       float* s, void* h_out, ql_stream_t stream);
+
+/*
+ * One-shot all-reduce over NVLink peer memory for RowParallelLinear's decode-sized outputs.
+ * Replaces `dist.all_reduce(y)` of RowParallelLinear.forward, nanovllm/layers/linear.py:150-152,
+ * when y ([M, hidden] bf16) is at most max_bytes; larger outputs stay on NCCL.  One communicator
+ * per process (the engine runs one process per GPU, model_runner.py:26-29).
+ *   ql_ar_init(max_bytes, world, rank, handle_out): cudaMalloc of this rank's receive area
+ *     (2 parities x world regions x 2*max_bytes), writes its CUDA IPC handle
+ *     (ql_ar_handle_bytes() bytes) to HOST memory handle_out;
+ *   the caller all-gathers the handles (torch.distributed) and passes the concatenation, in rank
+ *     order, to ql_ar_open (HOST pointer), which maps every peer's area;
+ *   ql_ar_allreduce_bf16(in, out, numel, stream): out[i] = bf16(sum over ranks r = 0..W-1 of
+ *     in_r[i], fp32, rank order); in/out are ordinary local device tensors (may alias); numel % 8
+ *     == 0, numel * 2 <= ql_ar_max_bytes(); stream-ordered, no host synchronisation, CUDA-graph
+ *     safe; every rank must issue the same sequence of calls.
+ * world in {2, 4, 8}.
+ */
+QL_API size_t ql_ar_handle_bytes(void);
+QL_API int ql_ar_init(size_t max_bytes, int world, int rank, void* handle_out);
+QL_API int ql_ar_open(const void* all_handles);
+QL_API size_t ql_ar_max_bytes(void);
+QL_API int ql_ar_allreduce_bf16(const void* in, void* out, int64_t numel, ql_stream_t stream);
 
 /* Bytes of caller-provided scratch ql_linear needs for an [M, K] activation (0 for M <= 16). */
 QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);

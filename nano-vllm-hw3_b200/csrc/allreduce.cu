@@ -1,0 +1,227 @@
+// One-shot all-reduce over NVLink peer memory for the row-parallel linears' decode-sized outputs
+// (SURVEY.md section 8e/8f-2).  Replaces the NCCL call of RowParallelLinear.forward
+// (nanovllm/layers/linear.py:150-152: `dist.all_reduce(y)`) when [M, hidden] bf16 is small: there
+// latency, not bandwidth, is the cost.
+//
+// Push protocol, no barriers and no fences: every rank owns a receive area (cudaMalloc + CUDA
+// IPC, mapped by all peers) with one region per (parity, source rank).  A thread loads 16 bytes
+// of its rank's partial sums, and for every peer stores them as two 16-byte packets
+// {data, epoch, data, epoch} straight into the peer's region (posted NVLink writes; data and flag
+// travel in the same store, so a packet whose two flags equal the call's epoch is complete).  It
+// then spins on the matching packets in its OWN region (local memory), adds the W partials in
+// fp32 in rank order -- identical on all ranks, deterministic, one rounding -- and stores bf16.
+// A first version (profiles/r1p_*) pulled the peers' data behind start/end flag barriers with
+// st.release.sys / ld.acquire.sys: 3 NVLink round trips + system fences per call made it slower
+// than NCCL.
+// Epochs live in device memory (one counter, advanced by the last block to finish), regions
+// alternate with the epoch's parity (a rank can be at most one call ahead of a peer: to start call
+// i+2 it needs the peer's packets of call i+1, which the peer sends after it has consumed call i),
+// so the kernel replays inside a CUDA graph.  No host synchronisation, no allocation per call.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ql {
+
+constexpr int kArMaxWorld = 8;
+constexpr int kArMaxBlocks = 64;
+constexpr int kArThreads = 256;
+
+struct ArState {
+  bool ready = false;
+  int world = 0, rank = 0;
+  size_t bytes = 0;                         // largest payload (bf16 bytes) of one call
+  uint8_t* local = nullptr;                 // this rank's receive area + counters
+  uint8_t* peer[kArMaxWorld] = {};          // everybody's area as mapped here (peer[rank] == local)
+};
+static ArState g_ar;
+
+// area layout: [parity 0: W regions of 2*bytes][parity 1: same][epoch u32][done u32]
+static size_t ar_region_bytes(size_t bytes) { return 2 * bytes; }          // 8 B packet per 4 B payload
+static size_t ar_ctr_offset(size_t bytes, int world) { return 2 * (size_t)world * ar_region_bytes(bytes); }
+static size_t ar_alloc_bytes(size_t bytes, int world) { return ar_ctr_offset(bytes, world) + 256; }
+
+struct ArParams {
+  uint8_t* area[kArMaxWorld];         // all ranks' receive areas
+  const uint4* in;                    // local partial sums (bf16)
+  uint4* out;                         // local bf16 output
+  uint32_t* ctr;                      // local {epoch, done}
+  int64_t nvec;                       // 16-byte payload vectors
+  size_t region;                      // bytes per (parity, source) region
+  int world, rank;
+};
+
+__device__ __forceinline__ void st_packet(void* p, uint32_t d0, uint32_t d1, uint32_t e) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(d0), "r"(e), "r"(d1),
+               "r"(e)
+               : "memory");
+}
+__device__ __forceinline__ uint4 ld_packet(const void* p) {
+  uint4 r;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+
+template <int W>
+__global__ void __launch_bounds__(kArThreads)
+ar_oneshot_kernel(const ArParams p) {
+  pdl_launch_dependents();
+  pdl_wait();                               // the partial sums come from the previous kernel (the GEMM)
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(p.ctr) + 1;
+  const size_t par = (size_t)(e & 1) * W * p.region;
+  const int64_t stride = (int64_t)gridDim.x * kArThreads;
+  const int64_t i0 = (int64_t)blockIdx.x * kArThreads + threadIdx.x;
+
+  // push: my vector i -> region (parity, my rank) of every peer, packets 2i and 2i+1
+  for (int64_t i = i0; i < p.nvec; i += stride) {
+    const uint4 v = p.in[i];
+#pragma unroll
+    for (int d = 1; d < W; ++d) {
+      const int r = (p.rank + d) % W;
+      uint8_t* dst = p.area[r] + par + (size_t)p.rank * p.region + (size_t)i * 32;
+      st_packet(dst, v.x, v.y, e);
+      st_packet(dst + 16, v.z, v.w, e);
+    }
+  }
+  // pull from my own area and reduce in rank order
+  for (int64_t i = i0; i < p.nvec; i += stride) {
+    const uint4 mine = p.in[i];
+    float acc[8];
+#pragma unroll
+    for (int r = 0; r < W; ++r) {
+      uint4 v;
+      if (r == p.rank) {
+        v = mine;
+      } else {
+        const uint8_t* src = p.area[p.rank] + par + (size_t)r * p.region + (size_t)i * 32;
+        uint4 a, b;
+        do { a = ld_packet(src); } while (a.y != e || a.w != e);
+        do { b = ld_packet(src + 16); } while (b.y != e || b.w != e);
+        v = make_uint4(a.x, a.z, b.x, b.z);
+      }
+      const float f[8] = {bf16_lo(v.x), bf16_hi(v.x), bf16_lo(v.y), bf16_hi(v.y),
+                          bf16_lo(v.z), bf16_hi(v.z), bf16_lo(v.w), bf16_hi(v.w)};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] = r == 0 ? f[k] : __fadd_rn(acc[k], f[k]);
+    }
+    uint4 o;
+    o.x = (uint32_t)f2bf(acc[0]) | ((uint32_t)f2bf(acc[1]) << 16);
+    o.y = (uint32_t)f2bf(acc[2]) | ((uint32_t)f2bf(acc[3]) << 16);
+    o.z = (uint32_t)f2bf(acc[4]) | ((uint32_t)f2bf(acc[5]) << 16);
+    o.w = (uint32_t)f2bf(acc[6]) | ((uint32_t)f2bf(acc[7]) << 16);
+    p.out[i] = o;
+  }
+  // the last block to finish publishes the epoch for the next call
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(p.ctr + 1, 1u) == gridDim.x - 1) {
+      p.ctr[1] = 0;
+      __threadfence();
+      *reinterpret_cast<volatile uint32_t*>(p.ctr) = e;
+    }
+  }
+}
+
+}  // namespace ql
+
+using namespace ql;
+
+extern "C" {
+
+size_t ql_ar_handle_bytes(void) { return sizeof(cudaIpcMemHandle_t); }
+
+int ql_ar_init(size_t max_bytes, int world, int rank, void* handle_out) {
+  if ((world != 2 && world != 4 && world != 8) || rank < 0 || rank >= world || max_bytes == 0 ||
+      max_bytes % 16 != 0)
+    return QL_ERR_BAD_SHAPE;
+  if (!handle_out) return QL_ERR_NULL;
+  if (g_ar.local != nullptr) return QL_ERR_BAD_SHAPE;   // one communicator per process (one process per GPU)
+  if (int e = ql_device_check()) return e;
+  const size_t total = ar_alloc_bytes(max_bytes, world);
+  uint8_t* ptr = nullptr;
+  if (cudaMalloc(&ptr, total) != cudaSuccess) { (void)cudaGetLastError(); return QL_ERR_CUDA; }
+  if (cudaMemset(ptr, 0, total) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
+    (void)cudaGetLastError();
+    cudaFree(ptr);
+    return QL_ERR_CUDA;
+  }
+  cudaIpcMemHandle_t h;
+  if (cudaIpcGetMemHandle(&h, ptr) != cudaSuccess) {
+    (void)cudaGetLastError();
+    cudaFree(ptr);
+    return QL_ERR_CUDA;
+  }
+  memcpy(handle_out, &h, sizeof(h));
+  g_ar.local = ptr;
+  g_ar.bytes = max_bytes;
+  g_ar.world = world;
+  g_ar.rank = rank;
+  return QL_OK;
+}
+
+int ql_ar_open(const void* all_handles) {
+  if (g_ar.local == nullptr) return QL_ERR_BAD_SHAPE;
+  if (!all_handles) return QL_ERR_NULL;
+  for (int r = 0; r < g_ar.world; ++r) {
+    if (r == g_ar.rank) { g_ar.peer[r] = g_ar.local; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const uint8_t*>(all_handles) + (size_t)r * sizeof(h), sizeof(h));
+    void* p = nullptr;
+    if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return QL_ERR_CUDA;
+    }
+    g_ar.peer[r] = static_cast<uint8_t*>(p);
+  }
+  g_ar.ready = true;
+  return QL_OK;
+}
+
+size_t ql_ar_max_bytes(void) { return g_ar.ready ? g_ar.bytes : 0; }
+
+int ql_ar_allreduce_bf16(const void* in, void* out, int64_t numel, ql_stream_t stream) {
+  if (!g_ar.ready) return QL_ERR_WORKSPACE;
+  if (numel < 0 || numel % 8 != 0 || (size_t)numel * 2 > g_ar.bytes) return QL_ERR_BAD_SHAPE;
+  if (numel == 0) return QL_OK;
+  if (!in || !out) return QL_ERR_NULL;
+  if ((uintptr_t)in % 16 != 0 || (uintptr_t)out % 16 != 0) return QL_ERR_MISALIGNED;
+  ArParams p;
+  for (int r = 0; r < kArMaxWorld; ++r) p.area[r] = r < g_ar.world ? g_ar.peer[r] : nullptr;
+  p.in = static_cast<const uint4*>(in);
+  p.out = static_cast<uint4*>(out);
+  p.ctr = reinterpret_cast<uint32_t*>(g_ar.local + ar_ctr_offset(g_ar.bytes, g_ar.world));
+  p.nvec = numel / 8;
+  p.region = ar_region_bytes(g_ar.bytes);
+  p.world = g_ar.world;
+  p.rank = g_ar.rank;
+  int64_t blocks = (p.nvec + kArThreads - 1) / kArThreads;
+  if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)blocks);
+  cfg.blockDim = dim3(kArThreads);
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t err;
+  switch (g_ar.world) {
+    case 2: err = cudaLaunchKernelEx(&cfg, ar_oneshot_kernel<2>, p); break;
+    case 4: err = cudaLaunchKernelEx(&cfg, ar_oneshot_kernel<4>, p); break;
+    default: err = cudaLaunchKernelEx(&cfg, ar_oneshot_kernel<8>, p); break;
+  }
+  count_launch();
+  if (err != cudaSuccess) { (void)cudaGetLastError(); return QL_ERR_CUDA; }
+  return QL_OK;
+}
+
+}  // extern "C"

@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libqlinear_b200.so")
 
 QL_INT8, QL_FP8_E4M3 = 0, 1
-QL_ABI_VERSION = 3
+QL_ABI_VERSION = 4
 _FMT = {torch.int8: QL_INT8, torch.float8_e4m3fn: QL_FP8_E4M3}
 
 _c_i64, _c_int, _c_vp, _c_sz = ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
@@ -44,6 +44,11 @@ SIGNATURES = {
     "ql_rmsnorm_quant": (_c_int, [_c_vp, _c_i64, _c_vp, _c_vp, _c_vp, ctypes.c_float, _c_i64, _c_i64,
                                   _c_int, _c_vp, _c_vp, _c_vp, _c_vp]),
     "ql_silu_mul_quant": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp, _c_vp]),
+    "ql_ar_handle_bytes": (_c_sz, []),
+    "ql_ar_init": (_c_int, [_c_sz, _c_int, _c_int, _c_vp]),
+    "ql_ar_open": (_c_int, [_c_vp]),
+    "ql_ar_max_bytes": (_c_sz, []),
+    "ql_ar_allreduce_bf16": (_c_int, [_c_vp, _c_vp, _c_i64, _c_vp]),
     "ql_workspace_bytes": (_c_sz, [_c_i64, _c_i64]),
     "ql_linear_path": (ctypes.c_char_p, [_c_i64, _c_i64, _c_i64, _c_i64]),
 }
@@ -186,14 +191,14 @@ def linear(x, qw, sw, bias, dtype, group_size: int = 0, out: torch.Tensor | None
 
 
 @torch.no_grad()
-def gemm_w8a8(qx, sx, qw, sw, bias, dtype, group_size: int = 0):
+def gemm_w8a8(qx, sx, qw, sw, bias, dtype, group_size: int = 0, out: torch.Tensor | None = None):
     """ql_gemm_w8a8 on pre-quantised activations (tcgen05 path regardless of M)."""
     fmt = fmt_of(dtype)
     assert qx.dtype == dtype and qw.dtype == dtype and qx.is_contiguous() and qw.is_contiguous()
     M, K = qx.shape
     N = qw.shape[0]
     assert K % 128 == 0, f"K({K}) must be multiple of BLK_K(128)"
-    y = torch.empty((M, N), dtype=torch.bfloat16, device=qx.device)
+    y = out if out is not None else torch.empty((M, N), dtype=torch.bfloat16, device=qx.device)
     with torch.cuda.device(qx.device):
         _check(load().ql_gemm_w8a8(_ptr(qx), _ptr(sx), _ptr(qw), _ptr(sw), _ptr(bias), _ptr(y), N,
                                    M, N, K, fmt, group_size, _stream(qx)))

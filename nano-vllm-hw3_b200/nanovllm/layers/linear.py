@@ -94,7 +94,7 @@ class LinearBase(nn.Module):
     def is_quantized(self) -> bool:
         return self.qw is not None
 
-    def _linear(self, x, bias: torch.Tensor | None) -> torch.Tensor:
+    def _linear(self, x, bias: torch.Tensor | None, out: torch.Tensor | None = None) -> torch.Tensor:
         if self.qw is None:
             return F.linear(x, self.weight, bias)
         b = None if bias is None else bias.data
@@ -102,8 +102,9 @@ class LinearBase(nn.Module):
             # QuantizedActivation from a fused producer (layers/layernorm.py, layers/activation.py):
             # this linear's per_row_quant launch is skipped
             assert x.q.dtype == self.qdtype, "producer and linear must use the same 8-bit format"
-            return _ext.gemm_w8a8(x.q, x.s, self.qw, self._sw_kernel, b, self.qdtype, self.group_size)
-        return _ext.linear(x, self.qw, self._sw_kernel, b, self.qdtype, self.group_size)
+            return _ext.gemm_w8a8(x.q, x.s, self.qw, self._sw_kernel, b, self.qdtype, self.group_size,
+                                  out=out)
+        return _ext.linear(x, self.qw, self._sw_kernel, b, self.qdtype, self.group_size, out=out)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         raise NotImplementedError
@@ -183,7 +184,17 @@ class RowParallelLinear(LinearBase):
         param.data.copy_(loaded_weight.narrow(self.tp_dim, self.tp_rank * shard, shard))
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        y = self._linear(x, self.bias if self.tp_rank == 0 else None)
+        bias = self.bias if self.tp_rank == 0 else None
+        y = self._linear(x, bias)
         if self.tp_size > 1:
-            dist.all_reduce(y)
+            comm = None
+            if self.qw is not None:
+                from nanovllm import _comm
+                comm = _comm.get()
+            if comm is not None and y.is_contiguous() and comm.fits(y.numel()):
+                # decode-sized output: one push-protocol kernel over NVLink peer memory
+                # (csrc/allreduce.cu) instead of the NCCL call
+                y = comm.all_reduce(y)
+            else:
+                dist.all_reduce(y)                       # reference linear.py:150-152
         return y
