@@ -303,6 +303,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+// wait + make the loaded registers depend on it, so that consumers of `r` cannot be scheduled
+// above the wait when other tcgen05.ld's are kept in flight around it
+__device__ __forceinline__ void tmem_ld_wait_regs(uint32_t (&r)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) asm volatile("" : "+r"(r[i]));
+}
 
 // K-major, 128-byte-swizzled shared-memory operand descriptor (sm_100 format):
 //   [0,14) start address >> 4 | [16,30) LBO >> 4 (unused for swizzled K-major) |

@@ -54,7 +54,13 @@ constexpr int kSmemBudget = 227 * 1024;
 // transpose the accumulator (feature on the TMEM lane) into token-major 16-byte global stores,
 // plus the 32 per-token scales of the chunk
 constexpr int kEpiWarpSmem = 32 * 32 * 2 + 32 * 4;
-constexpr int kEpiSmem = 4 * kEpiWarpSmem;
+constexpr int kEpiSmem = 8 * kEpiWarpSmem;   // up to 8 epilogue warps (per-group mode)
+// Per-group mode runs 8 epilogue warps (two per TMEM lane quarter, each promoting half of the token
+// columns): the per-K-block promotion, not the tensor core, bounds that mode.
+template <bool GROUPED, int BT> struct EpiCfg {
+  static constexpr int halves = (GROUPED && BT >= 64) ? 2 : 1;
+  static constexpr int threads = GROUPED ? 384 : 256;
+};
 
 template <int BT> struct GemmCfg {
   static constexpr int stage_a = kTileN * kBlockK;
@@ -71,7 +77,7 @@ template <int BT> struct GemmCfg {
 };
 
 template <int FMT, bool GROUPED, int BT, bool OUT_ACC>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(EpiCfg<GROUPED, BT>::threads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_x,
             const GemmParams p) {
   using Cfg = GemmCfg<BT>;
@@ -103,7 +109,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
     }
     for (int i = 0; i < NACC; ++i) {
       mbar_init(&tfull_bar[i], 1);
-      mbar_init(&tempty_bar[i], 4);  // one arrive per epilogue warp
+      mbar_init(&tempty_bar[i], 4 * EpiCfg<GROUPED, BT>::halves);  // one arrive per active epilogue warp
     }
     mbar_fence_init();
   }
@@ -203,9 +209,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
     }
   } else if (warp >= 4) {
     // ===================== epilogue (TMEM -> registers -> smem transpose -> global) ==========
-    const int q = warp - 4;  // TMEM lane quarter: this warp reads lanes [32q, 32q+32)
+    const int q = (warp - 4) & 3;   // TMEM lane quarter: this warp reads lanes [32q, 32q+32) (= warp % 4)
+    const int half = (warp - 4) >> 2;   // per-group mode: which half of the token columns
+    constexpr int HALVES = EpiCfg<GROUPED, BT>::halves;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-    uint16_t* stg = reinterpret_cast<uint16_t*>(epi_smem + q * kEpiWarpSmem);  // [32 m][32 n]
+    uint16_t* stg = reinterpret_cast<uint16_t*>(epi_smem + (warp - 4) * kEpiWarpSmem);  // [32 m][32 n]
     float* sxs = reinterpret_cast<float*>(stg + 32 * 32);                      // [32 m]
     const bool vec_ok = (p.ldy % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.y) & 15) == 0);
     int acc = 0;
@@ -304,10 +312,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty_bar[acc]);
         if (++acc == NACC) { acc = 0; acc_phase ^= 1; }
-      } else {
-        float t[BT];
+      } else if (half < HALVES) {
+        // per-group: this warp promotes token columns [half * CW, (half + 1) * CW) of every K block.
+        // The tcgen05.ld of chunk c+1 is in flight while chunk c is promoted.
+        constexpr int CW = BT / HALVES;
+        constexpr int NCH = CW / 32;
+        const uint32_t col0 = (uint32_t)(half * CW);
+        float t[CW];
 #pragma unroll
-        for (int i = 0; i < BT; ++i) t[i] = 0.0f;
+        for (int i = 0; i < CW; ++i) t[i] = 0.0f;
         const float* swrow = p.sw + (int64_t)(n_ok ? n : 0) * p.G;
         float sc = __ldg(swrow);
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -315,16 +328,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
           const float sc_next = __ldg(swrow + nxt);
           mbar_wait(&tfull_bar[acc], acc_phase);
           tc_fence_after();
+          uint32_t r[2][32];
+          tmem_ld32(lane_addr + acc * BT + col0, r[0]);
+          tmem_ld_wait_regs(r[0]);
 #pragma unroll
-          for (int c = 0; c < BT / 32; ++c) {
-            uint32_t r[32];
-            tmem_ld32(lane_addr + acc * BT + c * 32, r);
-            tmem_ld_wait();
+          for (int c = 0; c < NCH; ++c) {
+            if (c + 1 < NCH) tmem_ld32(lane_addr + acc * BT + col0 + (c + 1) * 32, r[(c + 1) & 1]);
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-              const float a = FMT == QL_INT8 ? __int2float_rn((int)r[i]) : __uint_as_float(r[i]);
+              const float a = FMT == QL_INT8 ? __int2float_rn((int)r[c & 1][i]) : __uint_as_float(r[c & 1][i]);
               t[c * 32 + i] = fmaf(a, sc, t[c * 32 + i]);
             }
+            if (c + 1 < NCH) tmem_ld_wait_regs(r[(c + 1) & 1]);
           }
           tc_fence_before();
           __syncwarp();
@@ -333,8 +348,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CU
           sc = sc_next;
         }
 #pragma unroll
-        for (int c = 0; c < BT / 32; ++c) {
-          const int mc = m0 + c * 32;
+        for (int c = 0; c < NCH; ++c) {
+          const int mc = m0 + (int)col0 + c * 32;
           if (mc < p.M) {
             sxs[lane] = (mc + lane < p.M) ? __ldg(p.sx + mc + lane) : 0.0f;
             __syncwarp();
@@ -419,7 +434,7 @@ static int launch_cfg(const void* qx, const void* qw, GemmParams p, cudaStream_t
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)grid);
-  cfg.blockDim = dim3(kGemmThreads);
+  cfg.blockDim = dim3(EpiCfg<GROUPED, BT>::threads);
   cfg.dynamicSmemBytes = Cfg::smem_bytes;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
