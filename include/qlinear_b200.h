@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define QL_ABI_VERSION 4
+#define QL_ABI_VERSION 5
 
 /* status codes */
 #define QL_OK 0
@@ -203,6 +203,21 @@ QL_API int ql_ar_init(size_t max_bytes, int world, int rank, void* handle_out);
 QL_API int ql_ar_open(const void* all_handles);
 QL_API size_t ql_ar_max_bytes(void);
 QL_API int ql_ar_allreduce_bf16(const void* in, void* out, int64_t numel, ql_stream_t stream);
+
+/*
+ * All-reduce fused with the residual add, RMSNorm and the per-token quantiser: everything between
+ * a row-parallel linear and the next column-parallel one in TP decode, in one kernel.
+ * Replaces dist.all_reduce(y) (nanovllm/layers/linear.py:150-152) + RMSNorm.add_rms_forward
+ * (nanovllm/layers/layernorm.py:27-40, called at models/qwen3.py:156-165) + per_row_quant
+ * (utils/quantization.py:147-163):
+ *   y = bf16(sum over ranks of partial_r, fp32, rank order)      == ql_ar_allreduce_bf16
+ *   (residual_out, q, s) = ql_rmsnorm_quant(y, residual_in, weight, eps)   (bit-identical)
+ * partial: this rank's un-reduced row-parallel output, bf16 [M, K] dense (K = hidden size, K % 8
+ * == 0, K <= 8192); M * K * 2 <= ql_ar_max_bytes().  Same calling rules as ql_ar_allreduce_bf16.
+ */
+QL_API int ql_ar_rmsnorm_quant(const void* partial, const void* residual_in, void* residual_out,
+                        const void* weight, float eps, int64_t M, int64_t K, int fmt, void* q,
+                        float* s, ql_stream_t stream);
 
 /* Bytes of caller-provided scratch ql_linear needs for an [M, K] activation (0 for M <= 16). */
 QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);

@@ -130,6 +130,17 @@ ar_oneshot_kernel(const ArParams p) {
   }
 }
 
+bool ar_view(ArView* v) {
+  if (!g_ar.ready) return false;
+  for (int r = 0; r < kArMaxWorld; ++r) v->area[r] = r < g_ar.world ? g_ar.peer[r] : nullptr;
+  v->ctr = reinterpret_cast<uint32_t*>(g_ar.local + ar_ctr_offset(g_ar.bytes, g_ar.world));
+  v->region = ar_region_bytes(g_ar.bytes);
+  v->max_bytes = g_ar.bytes;
+  v->world = g_ar.world;
+  v->rank = g_ar.rank;
+  return true;
+}
+
 }  // namespace ql
 
 using namespace ql;
@@ -222,6 +233,22 @@ int ql_ar_allreduce_bf16(const void* in, void* out, int64_t numel, ql_stream_t s
   count_launch();
   if (err != cudaSuccess) { (void)cudaGetLastError(); return QL_ERR_CUDA; }
   return QL_OK;
+}
+
+int ql_ar_rmsnorm_quant(const void* partial, const void* residual_in, void* residual_out,
+                        const void* weight, float eps, int64_t M, int64_t K, int fmt, void* q,
+                        float* s, ql_stream_t stream) {
+  if (fmt != QL_INT8 && fmt != QL_FP8_E4M3) return QL_ERR_BAD_FORMAT;
+  ArView ar;
+  if (!ar_view(&ar)) return QL_ERR_WORKSPACE;
+  if (M < 0 || K <= 0 || K % 8 != 0 || (size_t)M * (size_t)K * 2 > ar.max_bytes) return QL_ERR_BAD_SHAPE;
+  if (M == 0) return QL_OK;
+  if (!partial || !residual_in || !residual_out || !weight || !q || !s) return QL_ERR_NULL;
+  if ((uintptr_t)partial % 16 || (uintptr_t)residual_in % 16 || (uintptr_t)residual_out % 16 ||
+      (uintptr_t)weight % 16 || (uintptr_t)q % 8)
+    return QL_ERR_MISALIGNED;
+  return launch_ar_rmsnorm_quant(ar, partial, residual_in, residual_out, weight, eps, M, K, fmt, q, s,
+                                 (cudaStream_t)stream);
 }
 
 }  // extern "C"

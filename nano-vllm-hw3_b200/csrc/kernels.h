@@ -46,6 +46,19 @@ int launch_rmsnorm_quant(const void* x, int64_t ldx, const void* res_in, void* r
 int launch_silu_mul_quant(const void* gate_up, int64_t ld, int64_t M, int64_t I, int fmt, void* q,
                           float* s, void* h_out, cudaStream_t st);
 
+// Peer-memory communicator state (allreduce.cu), for kernels that fuse the all-reduce.
+struct ArView {
+  uint8_t* area[8];     // every rank's receive area as mapped in this process
+  uint32_t* ctr;        // local {epoch, done}
+  size_t region;        // bytes per (parity, source rank) region
+  size_t max_bytes;     // largest payload of one call
+  int world, rank;
+};
+bool ar_view(ArView* v);   // false until ql_ar_open succeeded
+int launch_ar_rmsnorm_quant(const ArView& ar, const void* partial, const void* res_in, void* res_out,
+                            const void* w, float eps, int64_t M, int64_t K, int fmt, void* q,
+                            float* s, cudaStream_t st);
+
 // CTA-pair (cta_group::2) tcgen05 GEMM for prefill-sized M, per-row scales only.
 int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* sw,
                  const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,

@@ -369,6 +369,149 @@ silu_mul_quant_kernel(const uint16_t* __restrict__ gu, int64_t ld, int64_t M, in
   }
 }
 
+// ---------------------------------------------------------------------------------- all-reduce + RMSNorm + quant
+// TP decode: o_proj / down_proj (row-parallel) -> all-reduce -> add residual -> RMSNorm -> quant for
+// the next qkv / gate_up (reference: linear.py:150-152, then models/qwen3.py:156-165).  One kernel:
+// the row layout of rmsnorm_quant_kernel with the one-shot push all-reduce of allreduce.cu as its
+// load stage -- every lane pushes its NV vectors of this rank's partial sums to the peers' receive
+// areas ({data, epoch} packets over NVLink), picks up the peers' packets for the same vectors from
+// its own area, adds them in fp32 in rank order and rounds to bf16 (bit-identical to the separate
+// all-reduce kernel), then continues as the RMSNorm producer.  Saves a launch and the bf16 round
+// trip of the reduced tensor per row-parallel linear.
+struct ArArgs {
+  uint8_t* area[8];
+  uint32_t* ctr;
+  size_t region;
+  int rank;
+};
+
+__device__ __forceinline__ void ar_st_packet(void* p, uint32_t d0, uint32_t d1, uint32_t e) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(d0), "r"(e), "r"(d1),
+               "r"(e)
+               : "memory");
+}
+__device__ __forceinline__ uint4 ar_ld_packet(const void* p) {
+  uint4 r;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+
+template <int FMT, int W, int NV, int WPR>
+__global__ void __launch_bounds__(RowCfg<WPR>::threads)
+ar_rmsnorm_quant_kernel(const ArArgs ar, const uint16_t* __restrict__ partial, const uint16_t* res_in,
+                        uint16_t* res_out, const uint16_t* __restrict__ w, float eps, int64_t M, int K,
+                        uint8_t* __restrict__ q, float* __restrict__ s) {
+  __shared__ float red[8];
+  pdl_launch_dependents();
+  pdl_wait();                               // the partial sums come from the row-parallel GEMM
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int ROWS = RowCfg<WPR>::rows;
+  const int64_t row = (int64_t)blockIdx.x * ROWS + warp / WPR;
+  const int part = warp % WPR;
+  const bool live = row < M;
+  const int64_t rowc = live ? row : 0;
+  const int nvec = K >> 3;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(ar.ctr) + 1;
+  const size_t par = (size_t)(e & 1) * W * ar.region;
+  const uint4* pr = reinterpret_cast<const uint4*>(partial + rowc * (int64_t)K);
+  const uint4* rr = reinterpret_cast<const uint4*>(res_in + rowc * (int64_t)K);
+  uint4* ro = reinterpret_cast<uint4*>(res_out + rowc * (int64_t)K);
+  const uint4* wv = reinterpret_cast<const uint4*>(w);
+
+  uint4 xv[NV], rv[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int idx = (i * WPR + part) * 32 + lane;
+    const bool ok = live && idx < nvec;
+    xv[i] = ok ? pr[idx] : make_uint4(0, 0, 0, 0);
+    rv[i] = ok ? rr[idx] : make_uint4(0, 0, 0, 0);
+    if (ok) {                               // push this rank's vector to every peer
+      const size_t off = par + (size_t)ar.rank * ar.region + (size_t)(rowc * nvec + idx) * 32;
+#pragma unroll
+      for (int d = 1; d < W; ++d) {
+        uint8_t* dst = ar.area[(ar.rank + d) % W] + off;
+        ar_st_packet(dst, xv[i].x, xv[i].y, e);
+        ar_st_packet(dst + 16, xv[i].z, xv[i].w, e);
+      }
+    }
+  }
+  float f[NV][8];
+  float ss = 0.0f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int idx = (i * WPR + part) * 32 + lane;
+    const bool ok = live && idx < nvec;
+    float acc[8];
+#pragma unroll
+    for (int r = 0; r < W; ++r) {           // fp32 sum in rank order, as ar_oneshot_kernel
+      uint4 v = xv[i];
+      if (r != ar.rank && ok) {
+        const uint8_t* src = ar.area[ar.rank] + par + (size_t)r * ar.region +
+                             (size_t)(rowc * nvec + idx) * 32;
+        uint4 a, b;
+        do { a = ar_ld_packet(src); } while (a.y != e || a.w != e);
+        do { b = ar_ld_packet(src + 16); } while (b.y != e || b.w != e);
+        v = make_uint4(a.x, a.z, b.x, b.z);
+      }
+      float g[8];
+      unpack8(v, g);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] = r == 0 ? g[k] : __fadd_rn(acc[k], g[k]);
+    }
+    unpack8(pack8(acc), f[i]);              // y = bf16(sum): what dist.all_reduce leaves in y
+    float g[8];
+    unpack8(rv[i], g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[i][k] = __fadd_rn(f[i][k], g[k]);
+    if (ok) ro[idx] = pack8(f[i]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) ss = __fadd_rn(ss, __fmul_rn(f[i][k], f[i][k]));
+  }
+  ss = row_reduce<WPR, false>(ss, red, warp);
+  const float rs = __frsqrt_rn(__fadd_rn(__fdiv_rn(ss, (float)K), eps));
+
+  uint4 hv[NV];
+  float amax = 0.0f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int idx = (i * WPR + part) * 32 + lane;
+    const bool ok = live && idx < nvec;
+    float g[8], h[8];
+    unpack8(ok ? __ldg(wv + idx) : make_uint4(0, 0, 0, 0), g);
+#pragma unroll
+    for (int k = 0; k < 8; k += 2) {
+      const uint32_t t = pack_bf(__fmul_rn(f[i][k], rs), __fmul_rn(f[i][k + 1], rs));
+      h[k] = __fmul_rn(bf16_lo(t), g[k]);
+      h[k + 1] = __fmul_rn(bf16_hi(t), g[k + 1]);
+    }
+    hv[i] = pack8(h);
+    amax = fmaxf(amax, amax8(hv[i]));
+  }
+  constexpr float qmax = FmtQ<FMT>::qmax;
+  amax = fmaxf(row_reduce<WPR, true>(amax, red, warp), 1e-8f);
+  const float inv = __fdiv_rn(qmax, amax);
+  if (live && part == 0 && lane == 0) s[row] = __fdiv_rn(amax, qmax);
+  uint2* qr = reinterpret_cast<uint2*>(q + rowc * (int64_t)K);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int idx = (i * WPR + part) * 32 + lane;
+    if (live && idx < nvec) qr[idx] = quant8_mul<FMT>(hv[i], inv);
+  }
+  // the last block to finish publishes the epoch for the next call (as ar_oneshot_kernel)
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(ar.ctr + 1, 1u) == gridDim.x - 1) {
+      ar.ctr[1] = 0;
+      __threadfence();
+      *reinterpret_cast<volatile uint32_t*>(ar.ctr) = e;
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------- host side
 
 static int block_threads(int nvec) { return nvec <= 128 ? 128 : nvec <= 1024 ? 256 : 512; }
@@ -489,6 +632,48 @@ int launch_silu_mul_quant(const void* gate_up, int64_t ld, int64_t M, int64_t I,
   if (q == nullptr) return launch_silu_fmt<QL_FMT_NONE>(gp, ld, M, (int)I, qp, s, hp, st);
   if (fmt == QL_INT8) return launch_silu_fmt<QL_INT8>(gp, ld, M, (int)I, qp, s, hp, st);
   return launch_silu_fmt<QL_FP8_E4M3>(gp, ld, M, (int)I, qp, s, hp, st);
+}
+
+template <int FMT, int W>
+static int launch_arn_fw(const ArArgs& a, const uint16_t* pp, const uint16_t* rp, uint16_t* rop,
+                         const uint16_t* wp, float eps, int64_t M, int K, uint8_t* qp, float* s,
+                         cudaStream_t st) {
+  int nv = 0, wpr = 0;
+  if (!pick_cfg(K / 8, 8, nv, wpr)) return QL_ERR_BAD_SHAPE;
+  const int rows_pb = wpr >= 4 ? 1 : 4 / wpr;
+  const int64_t blocks = (M + rows_pb - 1) / rows_pb;
+#define QL_ARN(NV, WPR)                                                                         \
+  if (nv == NV && wpr == WPR)                                                                   \
+    return launch_rows(ar_rmsnorm_quant_kernel<FMT, W, NV, WPR>, blocks, RowCfg<WPR>::threads, 0, \
+                       st, a, pp, rp, rop, wp, eps, M, K, qp, s)
+  QL_ARN(4, 1); QL_ARN(4, 2); QL_ARN(4, 4); QL_ARN(6, 4); QL_ARN(8, 4);
+#undef QL_ARN
+  return QL_ERR_BAD_SHAPE;               // rows longer than 8192 elements: use the unfused pair
+}
+
+int launch_ar_rmsnorm_quant(const ArView& ar, const void* partial, const void* res_in, void* res_out,
+                            const void* w, float eps, int64_t M, int64_t K, int fmt, void* q,
+                            float* s, cudaStream_t st) {
+  ArArgs a;
+  for (int r = 0; r < 8; ++r) a.area[r] = ar.area[r];
+  a.ctr = ar.ctr;
+  a.region = ar.region;
+  a.rank = ar.rank;
+  const auto* pp = static_cast<const uint16_t*>(partial);
+  const auto* rp = static_cast<const uint16_t*>(res_in);
+  auto* rop = static_cast<uint16_t*>(res_out);
+  const auto* wp = static_cast<const uint16_t*>(w);
+  auto* qp = static_cast<uint8_t*>(q);
+#define QL_ARN_W(F)                                                                              \
+  switch (ar.world) {                                                                            \
+    case 2: return launch_arn_fw<F, 2>(a, pp, rp, rop, wp, eps, M, (int)K, qp, s, st);           \
+    case 4: return launch_arn_fw<F, 4>(a, pp, rp, rop, wp, eps, M, (int)K, qp, s, st);           \
+    case 8: return launch_arn_fw<F, 8>(a, pp, rp, rop, wp, eps, M, (int)K, qp, s, st);           \
+    default: return QL_ERR_BAD_SHAPE;                                                            \
+  }
+  if (fmt == QL_INT8) { QL_ARN_W(QL_INT8) }
+  QL_ARN_W(QL_FP8_E4M3)
+#undef QL_ARN_W
 }
 
 }  // namespace ql

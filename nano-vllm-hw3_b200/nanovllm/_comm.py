@@ -49,6 +49,24 @@ class PeerAllReduce:
         return out
 
 
+    def fits_fused(self, M: int, K: int) -> bool:
+        return K % 8 == 0 and K <= 8192 and 0 < M * K * 2 <= self.bytes
+
+    @torch.no_grad()
+    def all_reduce_rmsnorm_quant(self, partial, residual, weight, eps: float, dtype):
+        """ql_ar_rmsnorm_quant: (q, s, new_residual) from this rank's un-reduced partial [M, K]."""
+        assert partial.dtype == torch.bfloat16 and partial.dim() == 2 and partial.is_contiguous()
+        M, K = partial.shape
+        assert residual.shape == partial.shape and residual.is_contiguous() and self.fits_fused(M, K)
+        q = torch.empty((M, K), dtype=dtype, device=partial.device)
+        s = torch.empty((M,), dtype=torch.float32, device=partial.device)
+        res = torch.empty_like(residual)
+        _ext._check(_ext.load().ql_ar_rmsnorm_quant(
+            partial.data_ptr(), residual.data_ptr(), res.data_ptr(), weight.data_ptr(), float(eps), M, K,
+            _ext.fmt_of(dtype), q.data_ptr(), s.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        return q, s, res
+
+
 def get() -> PeerAllReduce | None:
     """The process-wide communicator, created on first use (never during CUDA-graph capture:
     callers run one eager forward first, as the engine's warm-up does, model_runner.py:91-103)."""

@@ -59,9 +59,26 @@ class RMSNorm(nn.Module):
         h = h.view(x.shape)
         return h if residual is None else (h, res.view(x.shape))
 
-    def forward_quant(self, x: torch.Tensor, residual: torch.Tensor | None, dtype: torch.dtype):
+    def forward_quant(self, x: torch.Tensor, residual: torch.Tensor | None, dtype: torch.dtype,
+                      partial: bool = False):
         """As ``forward`` but returns the normalised activation quantised per token for the next
-        quantized linear: ``QuantizedActivation`` or ``(QuantizedActivation, residual)``."""
+        quantized linear: ``QuantizedActivation`` or ``(QuantizedActivation, residual)``.
+
+        ``partial=True`` (tensor parallel): ``x`` is this rank's UN-REDUCED row-parallel output
+        (``RowParallelLinear.forward_partial``); the all-reduce runs inside the same kernel
+        (``ql_ar_rmsnorm_quant``) when the batch is decode-sized, else NCCL + the plain kernel."""
+        if partial:
+            import torch.distributed as dist
+            from nanovllm import _comm
+            assert residual is not None
+            comm = _comm.get()
+            x2 = x.reshape(-1, x.shape[-1])
+            if comm is not None and x2.is_contiguous() and comm.fits_fused(*x2.shape):
+                q, s, res = comm.all_reduce_rmsnorm_quant(x2, residual.reshape(x2.shape).contiguous(),
+                                                          self.weight.data, self.eps, dtype)
+                return QuantizedActivation(q, s), res.view(x.shape)
+            x = x.clone()
+            dist.all_reduce(x)
         q, s, _, res = self._run(x, residual, dtype, False)
         qa = QuantizedActivation(q, s)
         return qa if residual is None else (qa, res.view(x.shape))

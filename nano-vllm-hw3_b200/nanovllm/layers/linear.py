@@ -183,6 +183,11 @@ class RowParallelLinear(LinearBase):
         shard = param.data.size(self.tp_dim)
         param.data.copy_(loaded_weight.narrow(self.tp_dim, self.tp_rank * shard, shard))
 
+    def forward_partial(self, x) -> torch.Tensor:
+        """This rank's un-reduced output (bias on rank 0 only): the input of the fused
+        all-reduce + RMSNorm + quant (`RMSNorm.forward_quant(..., partial=True)`)."""
+        return self._linear(x, self.bias if self.tp_rank == 0 else None)
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         bias = self.bias if self.tp_rank == 0 else None
         y = self._linear(x, bias)

@@ -81,6 +81,31 @@ def _worker(rank, world, port, q):
             g.replay()
         torch.cuda.synchronize()
         assert torch.equal(y1, ref) and torch.equal(y2, ref)
+        # fused all-reduce + add + RMSNorm + quant == the three separate steps, bit for bit
+        from nanovllm.layers.layernorm import RMSNorm
+        norm = RMSNorm(1024).cuda().to(torch.bfloat16)
+        norm.weight.data.normal_(1.0, 0.1, generator=torch.Generator(device="cuda").manual_seed(3))
+        for M in (1, 16, 130):
+            x = torch.randn(M, 3072 // world, device="cuda").to(torch.bfloat16)
+            resid = torch.randn(M, 1024, generator=torch.Generator().manual_seed(M)).to(torch.bfloat16).cuda()
+            qa_ref, res_ref = norm.forward_quant(layer(x), resid, torch.int8)
+            qa, res = norm.forward_quant(layer.forward_partial(x), resid, torch.int8, partial=True)
+            assert torch.equal(res, res_ref) and torch.equal(qa.q, qa_ref.q) and torch.equal(qa.s, qa_ref.s), M
+        gq = torch.cuda.CUDAGraph()
+        xg = torch.randn(16, 3072 // world, device="cuda").to(torch.bfloat16)
+        rg = torch.randn(16, 1024, generator=torch.Generator().manual_seed(99)).to(torch.bfloat16).cuda()
+        qa_ref, res_ref = norm.forward_quant(layer(xg), rg, torch.int8)
+        s2 = torch.cuda.Stream()
+        s2.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s2):
+            with torch.cuda.graph(gq, stream=s2):
+                qa_g, res_g = norm.forward_quant(layer.forward_partial(xg), rg, torch.int8, partial=True)
+                y_after = layer(xg)                               # plain all-reduce after the fused one
+        torch.cuda.current_stream().wait_stream(s2)
+        for _ in range(4):
+            gq.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(qa_g.q, qa_ref.q) and torch.equal(res_g, res_ref) and torch.equal(y_after, layer(xg))
         # larger than the symmetric buffer -> NCCL fallback still correct
         xb = torch.randn(2048, 3072 // world, device="cuda").to(torch.bfloat16)
         assert not comm.fits(2048 * 1024)
