@@ -222,7 +222,9 @@ def test_gemm_groups_vs_oracle(ext, dn, g, M, N, K):
 # ------------------------------------------------------------------ prefill regime: CTA-pair kernel
 
 PAIR_SHAPES = [(512, 4096, 128), (1024, 2048, 1024), (1000, 2072, 384), (777, 4096, 256),
-               (4096, 1024, 2048), (2304, 1032, 640)]
+               (4096, 1024, 2048), (2304, 1032, 640),
+               # 128 <= M < 512: dispatched to the pair kernel since round-1n (half-empty token tiles)
+               (128, 136, 256), (129, 520, 384), (200, 4096, 1024), (300, 1032, 640), (255, 256, 128)]
 
 
 @pytest.mark.parametrize("M,N,K", PAIR_SHAPES)

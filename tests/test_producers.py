@@ -210,3 +210,16 @@ def test_strided_gate_up_and_layers(ext):
     q1, s1, _ = ext.silu_mul_quant(wide[:, :2 * I], torch.int8)
     q2, s2, _ = ext.silu_mul_quant(wide[:, :2 * I].contiguous(), torch.int8)
     assert torch.equal(q1, q2) and torch.equal(s1, s2)
+
+
+@pytest.mark.gpu
+def test_producers_empty_batch(ext):
+    """M = 0 (an empty scheduler step): nothing is launched, shapes are kept."""
+    n0 = ext.launch_count()
+    w = torch.ones(1024, device="cuda", dtype=torch.bfloat16)
+    q, s, h = ext.rmsnorm_quant(torch.empty(0, 1024, device="cuda", dtype=torch.bfloat16), w, 1e-6, None,
+                                torch.int8, want_bf16=True)
+    assert q.shape == (0, 1024) and s.shape == (0,) and h.shape == (0, 1024)
+    q, s, _ = ext.silu_mul_quant(torch.empty(0, 6144, device="cuda", dtype=torch.bfloat16), torch.float8_e4m3fn)
+    assert q.shape == (0, 3072) and s.shape == (0,)
+    assert ext.launch_count() == n0
