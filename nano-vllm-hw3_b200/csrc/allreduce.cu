@@ -102,8 +102,9 @@ ar_oneshot_kernel(const ArParams p) {
       } else {
         const uint8_t* src = p.area[p.rank] + par + (size_t)r * p.region + (size_t)i * 32;
         uint4 a, b;
-        do { a = ld_packet(src); } while (a.y != e || a.w != e);
-        do { b = ld_packet(src + 16); } while (b.y != e || b.w != e);
+        SpinGuard guard;
+        while (true) { a = ld_packet(src); if (a.y == e && a.w == e) break; guard.tick(); }
+        while (true) { b = ld_packet(src + 16); if (b.y == e && b.w == e) break; guard.tick(); }
         v = make_uint4(a.x, a.z, b.x, b.z);
       }
       const float f[8] = {bf16_lo(v.x), bf16_hi(v.x), bf16_lo(v.y), bf16_hi(v.y),

@@ -198,6 +198,21 @@ __device__ __forceinline__ void mbar_wait_acq_cluster(uint64_t* bar, uint32_t pa
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
+// Bounded spin for cross-GPU flag waits: a peer that died must not hang this GPU forever.  After
+// ~10 s (globaltimer) the kernel traps, which surfaces as a CUDA error on the host -- loud, not silent.
+struct SpinGuard {
+  uint32_t n = 0;
+  uint64_t t0 = 0;
+  __device__ __forceinline__ void tick() {
+    if ((++n & 0xfffu) == 0) {
+      uint64_t t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      if (t0 == 0) t0 = t;
+      else if (t - t0 > 10000000000ull) __trap();
+    }
+  }
+};
+
 // Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization
 // attribute starts while its predecessor drains; everything that reads the predecessor's output
 // (or overwrites its input) must sit behind pdl_wait().  Both are no-ops for a plain launch.

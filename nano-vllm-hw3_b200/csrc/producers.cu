@@ -452,8 +452,9 @@ ar_rmsnorm_quant_kernel(const ArArgs ar, const uint16_t* __restrict__ partial, c
         const uint8_t* src = ar.area[ar.rank] + par + (size_t)r * ar.region +
                              (size_t)(rowc * nvec + idx) * 32;
         uint4 a, b;
-        do { a = ar_ld_packet(src); } while (a.y != e || a.w != e);
-        do { b = ar_ld_packet(src + 16); } while (b.y != e || b.w != e);
+        SpinGuard guard;
+        while (true) { a = ar_ld_packet(src); if (a.y == e && a.w == e) break; guard.tick(); }
+        while (true) { b = ar_ld_packet(src + 16); if (b.y == e && b.w == e) break; guard.tick(); }
         v = make_uint4(a.x, a.z, b.x, b.z);
       }
       float g[8];
