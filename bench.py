@@ -234,10 +234,12 @@ class LinearStack:
         return y
 
 
-def time_steps(fn, steps, warmup, dist_on):
+def time_steps(fn, steps, warmup, dist_on, finish=None):
     import torch.distributed as dist
     for _ in range(warmup):
         fn()
+    if finish is not None:
+        finish()
     if dist_on:
         dist.barrier()
     torch.cuda.synchronize()
@@ -245,6 +247,8 @@ def time_steps(fn, steps, warmup, dist_on):
     ev[0].record()
     for _ in range(steps):
         fn()
+    if finish is not None:
+        finish()                                           # the last step's D2H is inside the timed region
     ev[1].record()
     torch.cuda.synchronize()
     ms = ev[0].elapsed_time(ev[1])
@@ -395,15 +399,52 @@ def main():
             return graph_out["dev"][1]
         return stack.forward(x_dev)
 
+    # e2e: every step copies ITS input from pinned host memory and ITS result back to pinned host
+    # memory.  As a serving loop would, the copies run on their own streams and are double-buffered:
+    # the H2D of step i+1 and the D2H of step i-1 overlap the kernels of step i; the host reads
+    # (synchronises on) the result of the previous step while the current one runs.
+    cp_in, cp_out = torch.cuda.Stream(), torch.cuda.Stream()
+    stage_in = [torch.empty_like(x_dev) for _ in range(2)]
+    stage_out = [torch.empty_like(x_dev) for _ in range(2)]
+    y_hosts = [y_host, torch.empty_like(y_host).pin_memory()]
+    ev_in = [torch.cuda.Event() for _ in range(2)]
+    ev_free = [torch.cuda.Event() for _ in range(2)]
+    ev_done = [torch.cuda.Event() for _ in range(2)]
+    ev_out = [torch.cuda.Event() for _ in range(2)]
+    for e in ev_free + ev_out:
+        e.record()
+    e2e_i = [0]
+
     def step_e2e():
-        x_in.copy_(x_host, non_blocking=True)
+        i = e2e_i[0]
+        b = i & 1
+        e2e_i[0] = i + 1
+        main = torch.cuda.current_stream()
+        cp_in.wait_event(ev_free[b])                      # stage_in[b] was consumed two steps ago
+        with torch.cuda.stream(cp_in):
+            stage_in[b].copy_(x_host, non_blocking=True)  # H2D of this step's input
+            ev_in[b].record(cp_in)
+        main.wait_event(ev_in[b])
+        x_in.copy_(stage_in[b])
+        ev_free[b].record(main)
         if use_graph:
             graph_out["e2e"][0].replay()
             y = graph_out["e2e"][1]
         else:
             y = stack.forward(x_in)
-        y_host.copy_(y, non_blocking=True)
-        torch.cuda.current_stream().synchronize()         # the caller reads the result on the host
+        main.wait_event(ev_out[b])                        # stage_out[b] was read back two steps ago
+        stage_out[b].copy_(y)
+        ev_done[b].record(main)
+        cp_out.wait_event(ev_done[b])
+        with torch.cuda.stream(cp_out):
+            y_hosts[b].copy_(stage_out[b], non_blocking=True)   # D2H of this step's result
+            ev_out[b].record(cp_out)
+        if i > 0:
+            ev_out[1 - b].synchronize()                   # the caller reads the previous step's result
+
+    def finish_e2e():
+        for e in ev_out:
+            torch.cuda.current_stream().wait_event(e)
 
     sampler = ClockSampler(local) if rank == 0 else None
     n0 = _ext.launch_count()
@@ -411,7 +452,12 @@ def main():
     launches_per_step = _ext.launch_count() - n0
     ms = time_steps(step_dev, args.steps, args.warmup, dist_on)
     clocks = sampler.stop() if sampler else {}
-    ms_e2e = time_steps(step_e2e, args.steps, max(args.warmup, 3), dist_on)
+    ms_e2e = time_steps(step_e2e, args.steps, max(args.warmup, 3), dist_on, finish_e2e)
+    torch.cuda.synchronize()
+    # the pipelined leg must have produced the real result: same input as the resident leg
+    y_check = step_dev().float().cpu()
+    last = (e2e_i[0] - 1) & 1
+    assert torch.equal(y_hosts[last].float(), y_check), "e2e result differs from the resident-input result"
 
     # ---- dominant kernel alone (roofline): the GEMM (or GEMV for T <= 16) over all local weights
     shapes = layer_shapes(m, world)
@@ -477,6 +523,7 @@ def main():
                    "launch": "cuda graph replay" if use_graph else "eager"},
         "tflops": fl_layer * m["layers"] / (ms * 1e-3) / 1e12,
         "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
+                "pipeline": "double-buffered: H2D of step i+1 / D2H of step i-1 overlap the kernels of step i",
                 "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": y_host.numel() * 2},
         "gpu_launches": int(launches_per_step) * args.steps,
         "gpu_launches_per_step": int(launches_per_step),
