@@ -262,16 +262,28 @@ def time_steps(fn, steps, warmup, dist_on, finish=None):
 
 # ------------------------------------------------------------------ CPU arm
 
-def cpu_reference(m, T, dtype, quant, group, n_layers_sample, reps):
+def cpu_model_name():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def cpu_reference(m, T, dtype, quant, group, warmup, reps):
     """The reference's CPU quantized-linear path (per_group_quant + per_group_matmul with
     group_size = K for the per-row layout; quantization.py:194-234, 265-307) as restated in
-    oracle.ref_per_group_*; fp32 SGEMM on all host threads."""
+    oracle.ref_per_group_*: fp32 dequant + SGEMM on all host threads, ALL layers of the model,
+    T tokens per pass.  Returns (tokens/s, measured seconds per pass [list], threads)."""
     from oracle import oracle as orc
-    torch.set_num_threads(os.cpu_count() or 1)
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)          # torchrun exports OMP_NUM_THREADS=1: pin it explicitly
     g = torch.Generator().manual_seed(0)
     shapes = layer_shapes(m)
     layers = []
-    for _ in range(n_layers_sample):
+    for _ in range(m["layers"]):
         ws = []
         for _, N, K in shapes:
             w = (torch.randn(N, K, generator=g) * 0.02).to(torch.bfloat16)
@@ -288,16 +300,14 @@ def cpu_reference(m, T, dtype, quant, group, n_layers_sample, reps):
             h = orc.ref_per_group_matmul(h, gu[0][0], gu[0][1], None, gu[1], dtype)
             orc.ref_per_group_matmul(h[:, :k_down].contiguous(), dn[0][0], dn[0][1], None, dn[1], dtype)
 
-    one_pass()
+    for _ in range(warmup):
+        one_pass()
     ts = []
     for _ in range(reps):
         t0 = time.perf_counter()
         one_pass()
         ts.append(time.perf_counter() - t0)
-    ts.sort()
-    t_layer = ts[len(ts) // 2] / n_layers_sample
-    tok_s = T / (t_layer * m["layers"])
-    return tok_s, t_layer, torch.get_num_threads()
+    return T * len(ts) / sum(ts), ts, torch.get_num_threads()
 
 
 # ------------------------------------------------------------------ main
@@ -328,23 +338,36 @@ def main():
                 f"{m['layers']} layers), {args.dtype} {args.quant}"
                 + (f" g={group}" if group else "") + f", {T_rank} tokens/rank/step")
 
+    use_graph = not args.no_graph
+    config = {"workload": workload, "tokens_per_step": T_rank * world, "parallelism": f"tp{world}",
+              "l2": "one step streams every layer's distinct weights + activations (> 126 MB L2 "
+                    "working set for the default); no explicit flush",
+              "quant": args.quant, "group_size": group,
+              "launch": "cuda graph replay" if use_graph else "eager"}
+
     # ---------------------------------------------------------------- reference (CPU) arm
     if args.impl == "reference":
         if rank != 0:
             return
-        T_s = min(T_rank, 4096)
-        for _ in range(max(args.warmup - 1, 0)):
-            pass                                            # warm-up pass is inside cpu_reference
-        tok_s, t_layer, cores = cpu_reference(m, T_s, dtype, args.quant, group, 2, max(args.steps, 1))
+        # Every step is one MEASURED pass over all layers of the model on a bounded token sample
+        # (the CPU path's cost is linear in tokens); nothing is extrapolated across layers.
+        T_s = min(T_rank * world, 4096)
+        tok_s, ts, cores = cpu_reference(m, T_s, dtype, args.quant, group, min(max(args.warmup, 1), 2),
+                                         max(args.steps, 1))
+        ms_step = 1e3 * sum(ts) / len(ts)
+        sample = (f"every step = all {m['layers']} layers x {T_s} of the {T_rank * world} tokens of a step, "
+                  f"{len(ts)} timed steps (mean) after {min(max(args.warmup, 1), 2)} warm-up passes, torch fp32 dequant + SGEMM on {cores} threads of "
+                  f"{os.cpu_count()} host CPUs ({cpu_model_name()}); activations NOT quantised "
+                  "(the reference's per_group_matmul semantics)")
         line = {
             "impl": "reference", "metric": METRIC, "value": tok_s, "unit": "tokens/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_layer * m["layers"] * 1e3,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic (random-init weights, randn activations)",
-            "config": {"workload": workload, "arm": "reference CPU path: torch dequant + fp32 matmul"},
+            "data": "synthetic (random-init N(0,0.02) bf16 weights quantised on the host, randn activations)",
+            "config": config,
+            "reference_arm": "reference CPU path: torch dequant + fp32 matmul (oracle.ref_per_group_matmul)",
             "cpu_baseline": {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port",
-                             "sample": f"2 of {m['layers']} layers x {T_s} tokens per step, median of "
-                                       f"{max(args.steps, 1)} steps after 1 warm-up, scaled to {m['layers']} layers"},
+                             "sample": sample},
             "e2e": {"value": tok_s, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
         }
@@ -375,7 +398,6 @@ def main():
     # the reference engine replays its decode step (ModelRunner.capture_cudagraph,
     # model_runner.py:316-356); --no-graph launches the 2 x 112 kernels eagerly from Python, as the
     # reference does for prefill (model_runner.py:283-284) -- that mode is CPU-launch-bound.
-    use_graph = not args.no_graph
     graph_out = {}
 
     def capture(x_buf):
@@ -516,11 +538,7 @@ def main():
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "int8" if dtype == torch.int8 else "fp8_e4m3",
         "data": "synthetic (random-init N(0,0.02) bf16 weights quantised on device, randn activations)",
-        "config": {"workload": workload, "tokens_per_step": T, "parallelism": f"tp{world}",
-                   "l2": "one step streams every layer's distinct weights + activations (> 126 MB L2 "
-                         "working set for the default); no explicit flush",
-                   "quant": args.quant, "group_size": group,
-                   "launch": "cuda graph replay" if use_graph else "eager"},
+        "config": config,
         "tflops": fl_layer * m["layers"] / (ms * 1e-3) / 1e12,
         "e2e": {"value": T / (ms_e2e * 1e-3), "unit": "tokens/s", "ms_per_step": ms_e2e,
                 "pipeline": "double-buffered: H2D of step i+1 / D2H of step i-1 overlap the kernels of step i",
@@ -531,10 +549,11 @@ def main():
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         T_s = min(T_rank, 4096)
-        tok_s, t_layer, cores = cpu_reference(m, T_s, dtype, args.quant, group, 2, 3)
+        tok_s, ts, cores = cpu_reference(m, T_s, dtype, args.quant, group, 1, 2)
         line["cpu_baseline"] = {"value": tok_s, "unit": "tokens/s", "cores": cores, "kind": "port",
-                                "sample": f"2 of {m['layers']} layers x {T_s} tokens, median of 3 passes after "
-                                          f"1 warm-up, scaled to {m['layers']} layers"}
+                                "sample": f"all {m['layers']} layers x {T_s} tokens, mean of {len(ts)} measured passes "
+                                          f"after 1 warm-up ({cpu_model_name()}); activations not quantised "
+                                          "(reference per_group_matmul semantics)"}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist_on:

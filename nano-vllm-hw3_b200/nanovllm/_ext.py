@@ -235,22 +235,30 @@ def gemv_w8a8(x, qw, sw, bias, dtype, group_size: int = 0):
 
 
 @torch.no_grad()
-def rmsnorm_quant(x, weight, eps: float, residual=None, dtype=None, want_bf16: bool = False):
-    """ql_rmsnorm_quant.  x bf16 [M,K]; residual bf16 [M,K] or None (updated IN PLACE to x + residual,
-    as the engine's residual stream).  Returns (q, s, h): q/s None when dtype is None, h None
-    unless want_bf16 (or dtype is None)."""
+def rmsnorm_quant(x, weight, eps: float, residual=None, dtype=None, want_bf16: bool = False,
+                  residual_out=None):
+    """ql_rmsnorm_quant.  x bf16 [M,K]; residual bf16 [M,K] or None: x + residual is written to
+    ``residual_out`` (bf16 [M,K] dense) or, when that is None, IN PLACE over ``residual`` (the
+    engine's residual stream).  Returns (q, s, h): q/s None when dtype is None, h None unless
+    want_bf16 (or dtype is None)."""
     assert x.dtype == torch.bfloat16 and x.dim() == 2 and weight.dtype == torch.bfloat16
     _cuda_rowmajor(x, "x")
     M, K = x.shape
     assert weight.numel() == K and weight.is_contiguous()
     if residual is not None:
         assert residual.shape == x.shape and residual.dtype == torch.bfloat16 and residual.is_contiguous()
+        if residual_out is None:
+            residual_out = residual
+        assert residual_out.shape == x.shape and residual_out.dtype == torch.bfloat16 and \
+            residual_out.is_contiguous()
+    else:
+        assert residual_out is None
     fmt = fmt_of(dtype) if dtype is not None else 0
     q = torch.empty((M, K), dtype=dtype, device=x.device) if dtype is not None else None
     s = torch.empty((M,), dtype=torch.float32, device=x.device) if dtype is not None else None
     h = torch.empty((M, K), dtype=torch.bfloat16, device=x.device) if (want_bf16 or dtype is None) else None
     with torch.cuda.device(x.device):
-        _check(load().ql_rmsnorm_quant(_ptr(x), x.stride(0) if M > 1 else K, _ptr(residual), _ptr(residual),
+        _check(load().ql_rmsnorm_quant(_ptr(x), x.stride(0) if M > 1 else K, _ptr(residual), _ptr(residual_out),
                                        _ptr(weight), float(eps), M, K, fmt, _ptr(q), _ptr(s), _ptr(h),
                                        _stream(x)))
     return q, s, h

@@ -18,6 +18,7 @@ import torch.nn.functional as F
 from torch import nn
 
 from nanovllm import _ext
+from nanovllm.utils.context import get_context
 
 
 def _tp_rank_size():
@@ -57,11 +58,13 @@ class ParallelLMHead(nn.Module):
             self.weight = None
         return self
 
-    def forward(self, x: torch.Tensor, last_indices: torch.Tensor | None = None):
-        """``x`` bf16 [T, hidden] -> logits [T or len(last_indices), vocab] (rank 0; None elsewhere
-        under TP, as the reference :61-65).  ``last_indices`` replaces the reference's read of the
-        global prefill context (:56-59: ``context.cu_seqlens_q[1:] - 1``)."""
-        if last_indices is not None:
+    def forward(self, x: torch.Tensor):
+        """``x`` bf16 [T, hidden] -> logits (rank 0; None elsewhere under TP) -- the reference's
+        signature and behaviour, embed_head.py:56-66: during prefill (``get_context().is_prefill``)
+        only the last token of every sequence (``cu_seqlens_q[1:] - 1``) is projected."""
+        context = get_context()
+        if context.is_prefill:
+            last_indices = context.cu_seqlens_q[1:] - 1
             x = x[last_indices].contiguous()
         if self.qw is None:
             logits = F.linear(x, self.weight)

@@ -44,14 +44,19 @@ class RMSNorm(nn.Module):
         self.weight = nn.Parameter(torch.ones(hidden_size))
 
     def _run(self, x, residual, dtype, want_bf16):
-        shape = x.shape
-        x2 = x.reshape(-1, shape[-1])
+        K = x.shape[-1]
+        x2 = x.reshape(-1, K)
+        if x2.stride(-1) != 1 or (x2.shape[0] > 1 and x2.stride(0) % 8 != 0) or x2.data_ptr() % 16:
+            x2 = x2.contiguous()                  # the kernel needs 16-byte aligned, K-contiguous rows
+        res_out = None
         if residual is not None:
-            # add_rms_forward returns a NEW residual tensor (:34); the kernel updates a copy in
-            # place so the caller's tensor is not modified, as in the reference
-            residual = residual.reshape(-1, shape[-1]).clone()
-        q, s, h = _ext.rmsnorm_quant(x2, self.weight.data, self.eps, residual, dtype, want_bf16)
-        return q, s, h, residual
+            # add_rms_forward returns a NEW residual tensor (:34): the kernel writes x + residual
+            # into a fresh buffer, the caller's tensor is not modified
+            residual = residual.reshape(-1, K).contiguous()
+            res_out = torch.empty_like(residual)
+        q, s, h = _ext.rmsnorm_quant(x2, self.weight.data, self.eps, residual, dtype, want_bf16,
+                                     residual_out=res_out)
+        return q, s, h, res_out
 
     def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None):
         """bf16 in, bf16 out -- the reference's contract (:42-50)."""
