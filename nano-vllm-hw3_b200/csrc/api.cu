@@ -32,6 +32,19 @@ int num_sms() {
   return d.sms > 0 ? d.sms : 148;
 }
 
+int ensure_max_smem(const void* kern, int bytes, SmemAttrOnce& once) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return QL_ERR_CUDA;
+  const bool track = dev >= 0 && dev < 64;
+  if (track && __atomic_load_n(&once.done[dev], __ATOMIC_ACQUIRE)) return QL_OK;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return QL_ERR_CUDA;
+  }
+  if (track) __atomic_store_n(&once.done[dev], (unsigned char)1, __ATOMIC_RELEASE);
+  return QL_OK;
+}
+
 static unsigned long long g_launches = 0;
 void count_launch(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
 

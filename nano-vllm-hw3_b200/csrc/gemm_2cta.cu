@@ -415,13 +415,8 @@ template <int FMT, bool OUT_ACC, bool HAS_BIAS>
 static int launch_g2(const void* qx, const void* qw, void* y, int64_t ldy, Gemm2Params p,
                      cudaStream_t st) {
   auto kern = gemm2_kernel<FMT, OUT_ACC, HAS_BIAS>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kG2Smem) !=
-        cudaSuccess)
-      return QL_ERR_CUDA;
-    attr_set = true;
-  }
+  static SmemAttrOnce smem_once;   // per kernel instantiation, per device ordinal
+  if (int e = ensure_max_smem(reinterpret_cast<const void*>(kern), kG2Smem, smem_once)) return e;
   CUtensorMap tm_x, tm_w, tm_y;
   if (!make_tmap_2d(&tm_x, qx, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.M, p.K, kG2BlockK, kG2RowsA) ||
       !make_tmap_2d(&tm_w, qw, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.N, p.K, kG2BlockK, kG2RowsB))

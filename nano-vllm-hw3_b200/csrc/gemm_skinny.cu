@@ -584,13 +584,8 @@ static int launch_sk(const void* qx, const void* qw, SkinnyParams p, cudaStream_
   auto kern = skinny_kernel<FMT, GROUPED, BT, FUSED, OUT_ACC>;
   SkPlan pl;
   if (!plan_skinny<GROUPED, BT, FUSED>(p, pl)) return QL_ERR_BAD_SHAPE;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024) !=
-        cudaSuccess)
-      return QL_ERR_CUDA;
-    attr_set = true;
-  }
+  static SmemAttrOnce smem_once;   // per kernel instantiation, per device ordinal
+  if (int e = ensure_max_smem(reinterpret_cast<const void*>(kern), 226 * 1024, smem_once)) return e;
   CUtensorMap tm_w, tm_x;
   if (!make_tmap_2d(&tm_w, qw, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.N, p.K, kSkBlockK, kSkTileN))
     return QL_ERR_CUDA;

@@ -414,13 +414,8 @@ template <int FMT, bool GROUPED, int BT, bool OUT_ACC>
 static int launch_cfg(const void* qx, const void* qw, GemmParams p, cudaStream_t st) {
   using Cfg = GemmCfg<BT>;
   auto kern = gemm_kernel<FMT, GROUPED, BT, OUT_ACC>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes) !=
-        cudaSuccess)
-      return QL_ERR_CUDA;
-    attr_set = true;
-  }
+  static SmemAttrOnce smem_once;   // per kernel instantiation, per device ordinal
+  if (int e = ensure_max_smem(reinterpret_cast<const void*>(kern), Cfg::smem_bytes, smem_once)) return e;
   CUtensorMap tm_w, tm_x;
   if (!make_tmap(&tm_w, qw, p.N, p.K, kTileN) || !make_tmap(&tm_x, qx, p.M, p.K, BT))
     return QL_ERR_CUDA;

@@ -233,13 +233,8 @@ static int launch_one(const GemvParams& p, cudaStream_t st) {
   auto kern = gemv_kernel<FMT, GROUPED, MROWS, KSPLIT>;
   const size_t smem = (size_t)MROWS * (p.K + 16) + 64 + (KSPLIT > 1 ? 8 * 32 * 4 * 4 : 0);
   if (smem > 227 * 1024) return QL_ERR_BAD_SHAPE;
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) !=
-        cudaSuccess)
-      return QL_ERR_CUDA;
-    attr_set = true;
-  }
+  static SmemAttrOnce smem_once;   // per kernel instantiation, per device ordinal
+  if (int e = ensure_max_smem(reinterpret_cast<const void*>(kern), 227 * 1024, smem_once)) return e;
   const int64_t RG = ((int64_t)p.N + 7) / 8;
   const int64_t iters = (RG * KSPLIT + 7) / 8;
   int occ = (int)((220 * 1024) / smem);

@@ -74,6 +74,15 @@ bool make_tmap_2d(CUtensorMap* tm, const void* base, CUtensorMapDataType dt, int
 
 int num_sms();
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute and the library serves
+// several devices from one process (api.cu caches per ordinal, the binding switches devices per
+// call), so "set once" is tracked per device ordinal.  Setting it twice is harmless, so the
+// flags need no lock.
+struct SmemAttrOnce {
+  unsigned char done[64] = {};
+};
+int ensure_max_smem(const void* kern, int bytes, SmemAttrOnce& once);
+
 // Every kernel launch of the library bumps this (read through ql_launch_count()).
 void count_launch(int n = 1);
 

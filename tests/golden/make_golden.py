@@ -132,6 +132,29 @@ def main():
             out[f"pr_{tag}_{dn}_qw"], out[f"pr_{tag}_{dn}_sw"] = bits(qw), bits(sw)
             out[f"pr_{tag}_{dn}_y"] = bits(y)
 
+    # ---- F: long-K INT8 case: accumulators beyond 2^24, where tl.cast(acc, fp32) (:111) rounds ----
+    # K = 2048 with same-sign, near-full-scale rows: |acc| ~ 2048 * 120^2 = 2.9e7 > 2^24 and odd,
+    # so the int32 -> fp32 conversion is inexact and its rounding mode is pinned by this fixture.
+    M, N, K = 6, 24, 2048
+    x = randn(M, K)
+    w = randn(N, K, scale=0.02)
+    x[0] = 3.0                                                   # q = 127 everywhere
+    x[1] = (0.9 + 0.1 * torch.rand(K, generator=g)).to(torch.bfloat16) * 3.0
+    x[2] = -(0.9 + 0.1 * torch.rand(K, generator=g)).to(torch.bfloat16) * 2.0
+    w[0] = 0.02
+    w[1] = (0.9 + 0.1 * torch.rand(K, generator=g)).to(torch.bfloat16) * 0.02
+    w[2] = -(0.9 + 0.1 * torch.rand(K, generator=g)).to(torch.bfloat16) * 0.03
+    out["pr_d_x"], out["pr_d_w"] = bits(x), bits(w)
+    qx, sx = rq.per_row_quant(x, torch.int8)
+    qw, sw = rq.per_row_quant(w, torch.int8)
+    y = rq.per_row_matmul(x, qw, sw, None, torch.int8)
+    acc = qx[:3].int() @ qw[:3].int().T
+    assert int(acc.abs().max()) > (1 << 24) and bool((acc.abs() > (1 << 24)).sum() >= 8)
+    assert bool(((acc.abs() > (1 << 24)) & (acc % 2 != 0)).any()), "need an accumulator fp32 cannot hold"
+    out["pr_d_i8_qx"], out["pr_d_i8_sx"] = bits(qx), bits(sx)
+    out["pr_d_i8_qw"], out["pr_d_i8_sw"] = bits(qw), bits(sw)
+    out["pr_d_i8_y"] = bits(y)
+
     dst = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_golden.npz")
     np.savez_compressed(dst, **out)
     print(f"wrote {dst}: {len(out)} arrays, {os.path.getsize(dst)} bytes")

@@ -164,6 +164,28 @@ def test_gemm_i8_acc_bit_exact(ext, M, N, K):
 
 # ------------------------------------------------------------------ L2: scaled outputs
 
+def test_gemm_rows_golden_long_k_int8(ext, golden):
+    """Reference fixture d (K = 2048, |acc| > 2^24): every kernel family must reproduce the
+    reference's int32 -> fp32 rounding, hence its bf16 output, through the public entry points."""
+    p = "pr_d_i8_"
+    qx, qw, sx, sw = golden[p + "qx"], golden[p + "qw"], golden[p + "sx"], golden[p + "sw"]
+    yo, yf = orc.gemm_rows(qx, sx, qw, sw, None, orc.INT8, return_f32=True)
+    y = ext.gemm_w8a8(dev(qx, torch.int8), dev(sx, torch.float32), dev(qw, torch.int8),
+                      dev(sw, torch.float32), None, torch.int8)
+    assert np.array_equal(bits(y), yo)
+    assert bf16_ulp_diff(bits(y), golden[p + "y"]).max() <= 1      # interpreter truncates the last cast
+    y2 = ext.linear(dev(golden["pr_d_x"], torch.bfloat16), dev(qw, torch.int8), dev(sw, torch.float32),
+                    None, torch.int8)                              # quantiser + decode kernel
+    assert np.array_equal(bits(y2), yo)
+    acc = ext.gemm_i8_acc(dev(qx, torch.int8), dev(qw, torch.int8)).cpu().numpy()
+    assert np.array_equal(acc, orc.gemm_i8_acc(qx, qw)) and np.abs(acc).max() > (1 << 24)
+    # the same operands, repeated to a prefill-sized batch, through the CTA-pair kernel
+    rep = 64
+    yb = ext.gemm_w8a8(dev(np.tile(qx, (rep, 1)), torch.int8), dev(np.tile(sx, rep), torch.float32),
+                       dev(qw, torch.int8), dev(sw, torch.float32), None, torch.int8)
+    assert np.array_equal(bits(yb), np.tile(yo, (rep, 1)))
+
+
 @pytest.mark.parametrize("tag", ["a", "b", "c"])
 @pytest.mark.parametrize("dn", ["i8", "f8"])
 def test_gemm_rows_golden(ext, golden, tag, dn):
@@ -217,6 +239,41 @@ def test_gemm_groups_vs_oracle(ext, dn, g, M, N, K):
         assert np.array_equal(bits(y), yo)
     else:       # fp32 group sums: the cluster split-K kernel adds them in a different (fixed) order
         assert_close_fp(bits(y), yo)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("M,N,K,g", [(512, 4096, 1024, 128), (4096, 1024, 3072, 128), (4096, 6144, 1024, 128),
+                                     (1000, 520, 2048, 256)])
+def test_gemm_groups_prefill_sizes_vs_oracle(ext, dn, M, N, K, g):
+    """Per-group at the sizes it is benchmarked at (M >= 512: the tiled per-group GEMM, BT = 128/256
+    token tiles, 8 epilogue warps).  INT8: bit-exact (exact int32 group partials, the oracle's fmaf
+    promotion order); FP8: the stated tolerance."""
+    x, w = rand_bf16((M, K), M + N + g + 1), rand_bf16((N, K), K + N + g + 1, 0.02)
+    w[3, :g] *= 30.0
+    w[N - 1, K - g:] *= 0.01
+    b = rand_bf16((N,), 31)
+    qx, sx = orc.quant_rows(bits(x), FMT[dn])
+    qw, sw = orc.quant_groups(bits(w), g, FMT[dn])
+    assert not ext.linear_path(M, N, K, g).startswith("skinny")
+    y = ext.gemm_w8a8(dev(qx, DT[dn]), dev(sx, torch.float32), dev(qw, DT[dn]), dev(sw, torch.float32),
+                      b.cuda(), DT[dn], g)
+    yo = orc.gemm_groups(qx, sx, qw, sw, bits(b), g, FMT[dn])
+    if dn == "i8":
+        assert np.array_equal(bits(y), yo)
+    else:
+        assert_close_fp(bits(y), yo)
+
+
+def test_gemm_rows_fp8_full_size_vs_oracle(ext):
+    """FP8 per-row at a BASELINE prefill size (4096 x 4096 x 1024) against the oracle itself, not
+    only the reference's 8 % threshold."""
+    M, N, K = 4096, 4096, 1024
+    x, w = rand_bf16((M, K), 77), rand_bf16((N, K), 78, 0.02)
+    qx, sx = orc.quant_rows(bits(x), orc.FP8)
+    qw, sw = orc.quant_rows(bits(w), orc.FP8)
+    y = ext.gemm_w8a8(dev(qx, DT["f8"]), dev(sx, torch.float32), dev(qw, DT["f8"]), dev(sw, torch.float32),
+                      None, DT["f8"])
+    assert_close_fp(bits(y), orc.gemm_rows(qx, sx, qw, sw, None, orc.FP8))
 
 
 # ------------------------------------------------------------------ prefill regime: CTA-pair kernel

@@ -92,7 +92,7 @@ def _trunc_bf16(f32):
     return (np.ascontiguousarray(f32).view(np.uint32) >> 16).astype(np.uint16)
 
 
-@pytest.mark.parametrize("tag", ["a", "b", "c"])
+@pytest.mark.parametrize("tag", ["a", "b", "c", "d"])
 def test_triton_per_row_matmul_int8_bit_exact(golden, tag):
     """int32 accumulators and the fp32 epilogue (acc*sa*sb) are bit-exact vs the reference.
 
@@ -105,6 +105,22 @@ def test_triton_per_row_matmul_int8_bit_exact(golden, tag):
     assert np.array_equal(_trunc_bf16(yf), golden[p + "y"])
     assert np.array_equal(y, orc.bf16_encode(yf))
     assert bf16_ulp_diff(y, golden[p + "y"]).max() <= 1
+
+
+def test_long_k_fixture_pins_the_int32_to_fp32_cast(golden):
+    """Fixture d (K = 2048): accumulators beyond 2^24 that fp32 cannot hold -- the reference's
+    tl.cast(acc, fp32) (quantization.py:111) rounds, and the oracle must round the same way
+    (checked bit for bit by test_triton_per_row_matmul_int8_bit_exact[d]); here: the fixture
+    really contains such accumulators, and the quantiser part of it is pinned too."""
+    qx, qw = golden["pr_d_i8_qx"], golden["pr_d_i8_qw"]
+    assert qx.shape[1] == 2048
+    acc = orc.gemm_i8_acc(qx, qw)
+    big = np.abs(acc.astype(np.int64)) > (1 << 24)
+    inexact = big & (acc.astype(np.float32).astype(np.int64) != acc.astype(np.int64))
+    assert big.sum() >= 8 and inexact.sum() >= 1
+    for src, qk, sk in (("x", "qx", "sx"), ("w", "qw", "sw")):
+        q, s = orc.quant_rows(golden[f"pr_d_{src}"], orc.INT8)
+        assert np.array_equal(q, golden[f"pr_d_i8_{qk}"]) and np.array_equal(s, golden[f"pr_d_i8_{sk}"])
 
 
 @pytest.mark.parametrize("tag", ["a", "b", "c"])
