@@ -222,16 +222,21 @@ class LinearStack:
     def forward(self, x):
         """x bf16 [T, hidden] -> bf16 [T, hidden].  Attention / SiLU / norms are outside the
         hot path: the o_proj and down_proj inputs are the leading columns of the previous
-        output (a strided view, exercising ldx), and every layer starts from x again."""
+        output (a strided view, exercising ldx); every layer consumes the previous layer's output,
+        as the decoder stack does (qwen3.py:186-187).
+        Under tensor parallelism a row-parallel output that feeds the next quantized linear takes
+        the sequence-parallel hand-off (RowParallelLinear.forward_quant: GEMM-epilogue
+        reduce-scatter -> quantise the owner's tokens -> all-gather codes + scales); the last
+        linear returns the all-reduced bf16 tensor (RowParallelLinear.forward)."""
         m = self.m
         k_o, k_down = m["heads"] * m["hd"] // self.tp, m["inter"] // self.tp
-        y = x
-        for qkv, o, gate_up, down in self.layers:
-            h = qkv(x)
-            h = o(h[:, :k_o])
-            h = gate_up(h)
-            y = down(h[:, :k_down])
-        return y
+        h_in, last = x, len(self.layers) - 1
+        for i, (qkv, o, gate_up, down) in enumerate(self.layers):
+            h = qkv(h_in)
+            h = gate_up(o.forward_quant(h[:, :k_o]) if self.tp > 1 else o(h[:, :k_o]))
+            h = h[:, :k_down]
+            h_in = down.forward_quant(h) if (self.tp > 1 and i != last) else down(h)
+        return h_in
 
 
 def time_steps(fn, steps, warmup, dist_on, finish=None):
@@ -258,6 +263,86 @@ def time_steps(fn, steps, warmup, dist_on, finish=None):
         dist.barrier()
         ms = float(t.item())
     return ms / steps
+
+
+# ------------------------------------------------------------------ TP check, decode leg
+
+def tp_check(stack, T, dtype, rank, world):
+    """Run the collectives of the timed path on layer 0's o_proj and compare with their definition.
+    Raises (non-zero exit) on any mismatch; returns what ran."""
+    import torch.distributed as dist
+    from nanovllm import _comm, _ext
+    o = stack.layers[0][1]
+    comm = _comm.get()
+    info = {"status": "ok", "world": world, "checked": []}
+    K = o.qw.shape[1]
+    N = o.qw.shape[0]
+    for M in (T, 16 * world):
+        g = torch.Generator(device="cuda").manual_seed(100 + rank)
+        x = torch.randn(M, K, generator=g, device="cuda", dtype=torch.float32).to(torch.bfloat16)
+        part = o.forward_partial(x)
+        parts = [torch.empty_like(part) for _ in range(world)]
+        dist.all_gather(parts, part)
+        acc = parts[0].float()
+        for p in parts[1:]:
+            acc = acc + p.float()
+        y_def = acc.to(torch.bfloat16)
+        q_def, s_def = _ext.quant_rows(y_def, dtype)
+        qa = o.forward_quant(x)
+        y = o(x)
+        torch.cuda.synchronize()
+        if comm is None or not (comm.fits(M * N) or comm.fits_big(M, N)):
+            which = "nccl all_reduce (bf16 ring: tolerance check)"
+            ok = bool((y.float() - y_def.float()).abs().max() <= 2.0 ** -6 * y_def.float().abs().max())
+        else:
+            which = ("one-shot NVLink push all-reduce (ar_oneshot_kernel)" if comm.fits(M * N) else
+                     ("gemm2_push_kernel (GEMM epilogue -> peer TMA stores) + tp_reduce_kernel" if
+                      (comm.push and o.group_size == 0) else "tp_reduce_kernel (owners pull)"))
+            ok = bool(torch.equal(y, y_def) and torch.equal(qa.s, s_def)
+                      and torch.equal(qa.q.view(torch.uint8), q_def.view(torch.uint8)))
+        info["checked"].append({"tokens": M, "hidden": N, "collective": which, "bit_identical": ok})
+        flag = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if not bool(flag.item()):
+            info["status"] = "MISMATCH"
+            if rank == 0:
+                print(json.dumps({"tp_check": "MISMATCH", "detail": info}), flush=True)
+            torch.cuda.synchronize()
+            os._exit(3)
+    return info
+
+
+def decode_leg(stack, m, T, dtype, group, world, peaks, args, dist_on):
+    """The same stack at a decode-sized batch, CUDA-graph replay: HBM-bound (every weight byte is
+    streamed once per step), reported against the measured HBM peak."""
+    from nanovllm import _ext
+    gx = torch.Generator(device="cuda").manual_seed(2)
+    x = torch.randn(T, m["hidden"], generator=gx, device="cuda", dtype=torch.float32).to(torch.bfloat16)
+    n0 = _ext.launch_count()
+    stack.forward(x)
+    launches = _ext.launch_count() - n0
+    if not args.no_graph:
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=s):
+                stack.forward(x)
+        torch.cuda.current_stream().wait_stream(s)
+        fn = gr.replay
+    else:
+        def fn():
+            stack.forward(x)
+    ms = time_steps(fn, max(args.steps, 10), max(args.warmup, 3), dist_on)
+    shapes = layer_shapes(m, world)
+    _, by_layer = flops_bytes(T, shapes, group)
+    by = by_layer * m["layers"]
+    return {"tokens_per_step": T, "ms_per_step": ms, "value": T / (ms * 1e-3), "unit": "tokens/s",
+            "gpu_launches_per_step": int(launches), "bound": "hbm",
+            "algorithmic_bytes_per_step": by, "achieved_gbs": by / (ms * 1e-3) / 1e9,
+            "peak_gbs": peaks["hbm"], "frac": by / (ms * 1e-3) / 1e9 / peaks["hbm"],
+            "note": "whole step incl. quantisers and launch gaps, per rank; weights stream from HBM "
+                    "(the stack's distinct weights exceed L2)"}
 
 
 # ------------------------------------------------------------------ CPU arm
@@ -294,11 +379,12 @@ def cpu_reference(m, T, dtype, quant, group, warmup, reps):
     k_o, k_down = m["heads"] * m["hd"], m["inter"]
 
     def one_pass():
+        h_in = x
         for (qkv, o, gu, dn) in layers:
-            h = orc.ref_per_group_matmul(x, qkv[0][0], qkv[0][1], None, qkv[1], dtype)
+            h = orc.ref_per_group_matmul(h_in, qkv[0][0], qkv[0][1], None, qkv[1], dtype)
             h = orc.ref_per_group_matmul(h[:, :k_o].contiguous(), o[0][0], o[0][1], None, o[1], dtype)
             h = orc.ref_per_group_matmul(h, gu[0][0], gu[0][1], None, gu[1], dtype)
-            orc.ref_per_group_matmul(h[:, :k_down].contiguous(), dn[0][0], dn[0][1], None, dn[1], dtype)
+            h_in = orc.ref_per_group_matmul(h[:, :k_down].contiguous(), dn[0][0], dn[0][1], None, dn[1], dtype)
 
     for _ in range(warmup):
         one_pass()
@@ -481,6 +567,18 @@ def main():
     last = (e2e_i[0] - 1) & 1
     assert torch.equal(y_hosts[last].float(), y_check), "e2e result differs from the resident-input result"
 
+    # ---- multi-GPU correctness, visible in the line: the collective the timed path used, on one
+    # row-parallel layer, against its definition (fp32 rank-order sum of the gathered bf16 partials,
+    # rounded once; per_row_quant of that) -- bit for bit, prefill- and decode-sized
+    tp_info = None
+    if dist_on:
+        tp_info = tp_check(stack, T, dtype, rank, world)
+
+    # ---- decode-shaped leg (BASELINE.json configs[2] regime): the same stack at 16 tokens per rank
+    decode = None
+    if T_rank > 16:
+        decode = decode_leg(stack, m, 16 * world, dtype, group, world, peaks, args, dist_on)
+
     # ---- dominant kernel alone (roofline): the GEMM (or GEMV for T <= 16) over all local weights
     shapes = layer_shapes(m, world)
     fl_layer, by_layer = flops_bytes(T, shapes, group)
@@ -547,6 +645,11 @@ def main():
         "gpu_launches_per_step": int(launches_per_step),
         "roofline": roof, "clocks": clocks,
     }
+    if decode is not None:
+        line["decode"] = decode
+    if tp_info is not None:
+        line["tp_check"] = tp_info["status"]
+        line["tp_collective"] = tp_info
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         T_s = min(T_rank, 4096)
         tok_s, ts, cores = cpu_reference(m, T_s, dtype, args.quant, group, 1, 2)

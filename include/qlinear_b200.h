@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define QL_ABI_VERSION 5
+#define QL_ABI_VERSION 6
 
 /* status codes */
 #define QL_OK 0
@@ -187,20 +187,30 @@ QL_API int ql_silu_mul_quant(const void* gate_up, int64_t ld, int64_t M, int64_t
  * Replaces `dist.all_reduce(y)` of RowParallelLinear.forward, nanovllm/layers/linear.py:150-152,
  * when y ([M, hidden] bf16) is at most max_bytes; larger outputs stay on NCCL.  One communicator
  * per process (the engine runs one process per GPU, model_runner.py:26-29).
- *   ql_ar_init(max_bytes, world, rank, handle_out): cudaMalloc of this rank's receive area
- *     (2 parities x world regions x 2*max_bytes), writes its CUDA IPC handle
- *     (ql_ar_handle_bytes() bytes) to HOST memory handle_out;
+ *   ql_ar_can_access_peers(world): QL_OK when the current device can map the memory of devices
+ *     0..world-1 (one process per GPU, rank == device ordinal); call before ql_ar_init and fall back
+ *     to NCCL on every rank if any rank says no;
+ *   ql_ar_init(max_bytes, rs_tokens, rs_hidden, world, rank, handle_out): cudaMalloc of this rank's
+ *     symmetric area -- 2 parities x world regions x 2*max_bytes for the one-shot all-reduce, plus,
+ *     when rs_tokens > 0, the buffers of the large path (ql_tp_*) for [rs_tokens, rs_hidden]
+ *     outputs -- and writes its CUDA IPC handle (ql_ar_handle_bytes() bytes) to HOST memory;
  *   the caller all-gathers the handles (torch.distributed) and passes the concatenation, in rank
  *     order, to ql_ar_open (HOST pointer), which maps every peer's area;
+ *   ql_ar_destroy(): unmaps the peers and frees the area (failed set-up, shutdown); idempotent;
  *   ql_ar_allreduce_bf16(in, out, numel, stream): out[i] = bf16(sum over ranks r = 0..W-1 of
  *     in_r[i], fp32, rank order); in/out are ordinary local device tensors (may alias); numel % 8
  *     == 0, numel * 2 <= ql_ar_max_bytes(); stream-ordered, no host synchronisation, CUDA-graph
  *     safe; every rank must issue the same sequence of calls.
- * world in {2, 4, 8}.
+ * world in {2, 4, 8}.  Flag waits are bounded by QL_AR_TIMEOUT_S seconds (default 10, 0 = wait
+ * forever): past it the kernel traps (CUDA error) instead of hanging on a dead peer.  These kernels
+ * cannot be profiled with ncu kernel replay (a replayed launch never sees matching epochs).
  */
 QL_API size_t ql_ar_handle_bytes(void);
-QL_API int ql_ar_init(size_t max_bytes, int world, int rank, void* handle_out);
+QL_API int ql_ar_can_access_peers(int world);
+QL_API int ql_ar_init(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int world, int rank,
+               void* handle_out);
 QL_API int ql_ar_open(const void* all_handles);
+QL_API int ql_ar_destroy(void);
 QL_API size_t ql_ar_max_bytes(void);
 QL_API int ql_ar_allreduce_bf16(const void* in, void* out, int64_t numel, ql_stream_t stream);
 
@@ -218,6 +228,50 @@ QL_API int ql_ar_allreduce_bf16(const void* in, void* out, int64_t numel, ql_str
 QL_API int ql_ar_rmsnorm_quant(const void* partial, const void* residual_in, void* residual_out,
                         const void* weight, float eps, int64_t M, int64_t K, int fmt, void* q,
                         float* s, ql_stream_t stream);
+
+/*
+ * Prefill-sized row-parallel outputs under tensor parallelism: reduce-scatter + per-token quantiser
+ * + all-gather over NVLink peer memory (csrc/tp_collective.cu, csrc/gemm_2cta.cu).
+ * Replaces `dist.all_reduce(y)` of RowParallelLinear.forward (nanovllm/layers/linear.py:150-152)
+ * and the `per_row_quant(x)` of the NEXT quantized linear (utils/quantization.py:147-163, :323):
+ * tokens are owned by ranks in slices of whole 256-token tiles; the owner adds the W bf16 partials
+ * in fp32 in rank order, rounds once to bf16, quantises its tokens and sends codes + scales to
+ * every rank, whose next column-parallel GEMM reads them through ql_gemm_w8a8.
+ *   ql_tp_max_tokens / ql_tp_max_hidden: capacity given to ql_ar_init (0 = path unavailable);
+ *   ql_tp_buffer(which): this rank's buffers inside the symmetric area (device pointers that stay
+ *     valid until ql_ar_destroy): 0 = bf16 partial [M, N] dense (write the row-parallel GEMM's
+ *     output here for pushed = 0), 1 = gathered codes [M, N], 2 = gathered scales fp32 [M];
+ *   ql_tp_gemm_push: the row-parallel W8A8 GEMM (per-row scales, as ql_gemm_w8a8) whose epilogue
+ *     TMA-stores every 256-token tile into the receive region of the rank that owns those tokens --
+ *     GEMM and reduce-scatter in ONE kernel, the transfer overlapping the remaining tiles;
+ *   ql_tp_reduce_quant_gather(M, N, fmt, pushed): after it (stream-ordered) buffers 1 and 2 hold
+ *     ql_quant_rows(bf16(sum of the ranks' partials)) for all M tokens on every rank, bit-identical
+ *     to all-reduce (fp32, rank order) followed by ql_quant_rows.  pushed = 1: partials came from
+ *     ql_tp_gemm_push; pushed = 0: every rank left its partial in buffer 0 and the owners pull;
+ *   ql_tp_allreduce_bf16(M, N, pushed, out, ldo): same reduction, bf16 rows gathered instead; the
+ *     complete [M, N] result is written to the local tensor `out` (dist.all_reduce semantics).
+ * M <= ql_tp_max_tokens(), N <= ql_tp_max_hidden(), N % 8 == 0.  Same calling rules as
+ * ql_ar_allreduce_bf16 (every rank, same order, same shapes; CUDA-graph safe).
+ */
+/*
+ * Test hook: a W-rank communicator emulated on ONE GPU (the driver's GPU test tier has a single
+ * GPU).  ql_ar_init_local allocates all W symmetric areas in this process; ql_tp_emu_set_rank(r)
+ * makes the following ql_tp_gemm_push / ql_tp_buffer calls act as rank r; ql_tp_reduce_quant_gather /
+ * ql_tp_allreduce_bf16 then run ALL ranks in one co-resident launch (for the bf16 form `out` holds W
+ * stacked [M, ldo] tensors).  Same kernels, same flags, same tensor maps as the multi-GPU path --
+ * only the addresses are local.  Not part of the reference-facing surface.
+ */
+QL_API int ql_ar_init_local(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int world);
+QL_API int ql_tp_emu_set_rank(int rank);
+
+QL_API size_t ql_tp_max_tokens(void);
+QL_API size_t ql_tp_max_hidden(void);
+QL_API void* ql_tp_buffer(int which);
+QL_API int ql_tp_gemm_push(const void* qx, const float* sx, const void* qw, const float* sw,
+                    const void* bias, int64_t M, int64_t N, int64_t K, int fmt, ql_stream_t stream);
+QL_API int ql_tp_reduce_quant_gather(int64_t M, int64_t N, int fmt, int pushed, ql_stream_t stream);
+QL_API int ql_tp_allreduce_bf16(int64_t M, int64_t N, int pushed, void* out, int64_t ldo,
+                         ql_stream_t stream);
 
 /* Bytes of caller-provided scratch ql_linear needs for an [M, K] activation (0 for M <= 16). */
 QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);

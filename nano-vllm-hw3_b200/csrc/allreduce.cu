@@ -20,6 +20,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -33,17 +34,41 @@ constexpr int kArThreads = 256;
 
 struct ArState {
   bool ready = false;
+  bool emulated = false;                    // all W areas live in THIS process (ql_ar_init_local)
   int world = 0, rank = 0;
-  size_t bytes = 0;                         // largest payload (bf16 bytes) of one call
+  size_t bytes = 0;                         // largest payload (bf16 bytes) of one one-shot call
+  size_t big_rows = 0, big_hidden = 0;      // capacity of the large (reduce-scatter) path, 0 = off
   uint8_t* local = nullptr;                 // this rank's receive area + counters
   uint8_t* peer[kArMaxWorld] = {};          // everybody's area as mapped here (peer[rank] == local)
 };
 static ArState g_ar;
 
-// area layout: [parity 0: W regions of 2*bytes][parity 1: same][epoch u32][done u32]
+// area layout: [parity 0: W regions of 2*bytes][parity 1: same][epoch u32][done u32] (256 B)
+//              [big section, 4 KB aligned: flags 4 KB | partial | codes | scales | bf16 gather]
 static size_t ar_region_bytes(size_t bytes) { return 2 * bytes; }          // 8 B packet per 4 B payload
 static size_t ar_ctr_offset(size_t bytes, int world) { return 2 * (size_t)world * ar_region_bytes(bytes); }
-static size_t ar_alloc_bytes(size_t bytes, int world) { return ar_ctr_offset(bytes, world) + 256; }
+static size_t ar_big_offset(size_t bytes, int world) { return (ar_ctr_offset(bytes, world) + 256 + 4095) & ~(size_t)4095; }
+static size_t rup(size_t v, size_t a) { return (v + a - 1) / a * a; }
+// rows of the partial / receive buffer: every owner's slice is rounded up to whole 256-token tiles
+static size_t big_rows_cap(size_t rows, int world) { return rup(rows, 256) + 256 * (size_t)world; }
+static void big_layout(size_t rows, size_t hidden, int world, TpLayout* L) {
+  const size_t cap = big_rows_cap(rows, world);
+  L->flags = 0;
+  L->part = 4096;
+  L->q = L->part + rup(cap * hidden * 2, 1024);
+  L->s = L->q + rup(cap * hidden, 1024);
+  L->y = L->s + rup(cap * 4, 1024);
+  L->total = L->y + rup(cap * hidden * 2, 1024);
+}
+static size_t ar_alloc_bytes(size_t bytes, int world, size_t rows, size_t hidden) {
+  size_t total = ar_big_offset(bytes, world);
+  if (rows > 0 && hidden > 0) {
+    TpLayout L;
+    big_layout(rows, hidden, world, &L);
+    total += L.total;
+  }
+  return total;
+}
 
 struct ArParams {
   uint8_t* area[kArMaxWorld];         // all ranks' receive areas
@@ -52,6 +77,7 @@ struct ArParams {
   uint32_t* ctr;                      // local {epoch, done}
   int64_t nvec;                       // 16-byte payload vectors
   size_t region;                      // bytes per (parity, source) region
+  uint64_t timeout_ns;                // flag-wait bound (QL_AR_TIMEOUT_S; 0 = wait forever)
   int world, rank;
 };
 
@@ -102,7 +128,7 @@ ar_oneshot_kernel(const ArParams p) {
       } else {
         const uint8_t* src = p.area[p.rank] + par + (size_t)r * p.region + (size_t)i * 32;
         uint4 a, b;
-        SpinGuard guard;
+        SpinGuard guard(p.timeout_ns);
         while (true) { a = ld_packet(src); if (a.y == e && a.w == e) break; guard.tick(); }
         while (true) { b = ld_packet(src + 16); if (b.y == e && b.w == e) break; guard.tick(); }
         v = make_uint4(a.x, a.z, b.x, b.z);
@@ -131,6 +157,16 @@ ar_oneshot_kernel(const ArParams p) {
   }
 }
 
+uint64_t ar_timeout_ns() {
+  static long long v = -1;
+  if (v < 0) {
+    const char* e = getenv("QL_AR_TIMEOUT_S");
+    const double sec = (e != nullptr && e[0] != 0) ? atof(e) : 10.0;
+    v = sec <= 0.0 ? 0 : (long long)(sec * 1e9);
+  }
+  return (uint64_t)v;
+}
+
 bool ar_view(ArView* v) {
   if (!g_ar.ready) return false;
   for (int r = 0; r < kArMaxWorld; ++r) v->area[r] = r < g_ar.world ? g_ar.peer[r] : nullptr;
@@ -139,6 +175,22 @@ bool ar_view(ArView* v) {
   v->max_bytes = g_ar.bytes;
   v->world = g_ar.world;
   v->rank = g_ar.rank;
+  v->timeout_ns = ar_timeout_ns();
+  return true;
+}
+
+bool tp_view(TpView* v) {
+  if (!g_ar.ready || g_ar.big_rows == 0) return false;
+  const size_t off = ar_big_offset(g_ar.bytes, g_ar.world);
+  for (int r = 0; r < kArMaxWorld; ++r) v->big[r] = r < g_ar.world ? g_ar.peer[r] + off : nullptr;
+  big_layout(g_ar.big_rows, g_ar.big_hidden, g_ar.world, &v->lay);
+  v->rows = g_ar.big_rows;
+  v->rows_cap = big_rows_cap(g_ar.big_rows, g_ar.world);
+  v->hidden = g_ar.big_hidden;
+  v->world = g_ar.world;
+  v->rank = g_ar.rank;
+  v->emulated = g_ar.emulated;
+  v->timeout_ns = ar_timeout_ns();
   return true;
 }
 
@@ -150,17 +202,38 @@ extern "C" {
 
 size_t ql_ar_handle_bytes(void) { return sizeof(cudaIpcMemHandle_t); }
 
-int ql_ar_init(size_t max_bytes, int world, int rank, void* handle_out) {
+int ql_ar_can_access_peers(int world) {
+  if (world < 1 || world > kArMaxWorld) return QL_ERR_BAD_SHAPE;
+  if (int e = ql_device_check()) return e;
+  int dev = 0, count = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceCount(&count) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return QL_ERR_CUDA;
+  }
+  if (count < world) return QL_ERR_UNSUPPORTED_ARCH;
+  // one process per GPU, rank == device ordinal on the node (model_runner.py:29)
+  for (int d = 0; d < world; ++d) {
+    if (d == dev) continue;
+    int ok = 0;
+    if (cudaDeviceCanAccessPeer(&ok, dev, d) != cudaSuccess) { (void)cudaGetLastError(); return QL_ERR_CUDA; }
+    if (!ok) return QL_ERR_UNSUPPORTED_ARCH;
+  }
+  return QL_OK;
+}
+
+int ql_ar_init(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int world, int rank, void* handle_out) {
   if ((world != 2 && world != 4 && world != 8) || rank < 0 || rank >= world || max_bytes == 0 ||
-      max_bytes % 16 != 0)
+      max_bytes % 16 != 0 || rs_hidden % 8 != 0 || (rs_tokens == 0) != (rs_hidden == 0))
     return QL_ERR_BAD_SHAPE;
   if (!handle_out) return QL_ERR_NULL;
   if (g_ar.local != nullptr) return QL_ERR_BAD_SHAPE;   // one communicator per process (one process per GPU)
   if (int e = ql_device_check()) return e;
-  const size_t total = ar_alloc_bytes(max_bytes, world);
+  const size_t total = ar_alloc_bytes(max_bytes, world, rs_tokens, rs_hidden);
   uint8_t* ptr = nullptr;
   if (cudaMalloc(&ptr, total) != cudaSuccess) { (void)cudaGetLastError(); return QL_ERR_CUDA; }
-  if (cudaMemset(ptr, 0, total) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
+  // only the packet regions, counters and flags need a defined initial state (epoch 0)
+  const size_t head = ar_big_offset(max_bytes, world) + (rs_tokens ? 4096 : 0);
+  if (cudaMemset(ptr, 0, head) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
     (void)cudaGetLastError();
     cudaFree(ptr);
     return QL_ERR_CUDA;
@@ -174,6 +247,8 @@ int ql_ar_init(size_t max_bytes, int world, int rank, void* handle_out) {
   memcpy(handle_out, &h, sizeof(h));
   g_ar.local = ptr;
   g_ar.bytes = max_bytes;
+  g_ar.big_rows = rs_tokens;
+  g_ar.big_hidden = rs_hidden;
   g_ar.world = world;
   g_ar.rank = rank;
   return QL_OK;
@@ -197,10 +272,75 @@ int ql_ar_open(const void* all_handles) {
   return QL_OK;
 }
 
+// Single-GPU emulation of a W-rank communicator for tests (the GPU test tier has one GPU): all W
+// symmetric areas are allocated in this process; ql_tp_emu_set_rank selects which rank the next
+// ql_tp_gemm_push / ql_tp_buffer call acts as, and the reduce kernels run ALL ranks in one launch
+// (blockIdx.y = rank, co-resident grid) -- kernels that wait on one another must never be separate
+// launches on one GPU.  Only the prefill-sized path (ql_tp_*) is emulated.
+int ql_ar_init_local(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int world) {
+  if ((world != 2 && world != 4 && world != 8) || max_bytes == 0 || max_bytes % 16 != 0 || rs_tokens == 0 ||
+      rs_hidden == 0 || rs_hidden % 8 != 0)
+    return QL_ERR_BAD_SHAPE;
+  if (g_ar.local != nullptr) return QL_ERR_BAD_SHAPE;
+  if (int e = ql_device_check()) return e;
+  const size_t total = ar_alloc_bytes(max_bytes, world, rs_tokens, rs_hidden);
+  const size_t head = ar_big_offset(max_bytes, world) + 4096;
+  for (int r = 0; r < world; ++r) {
+    uint8_t* ptr = nullptr;
+    if (cudaMalloc(&ptr, total) != cudaSuccess || cudaMemset(ptr, 0, head) != cudaSuccess) {
+      (void)cudaGetLastError();
+      if (ptr != nullptr) cudaFree(ptr);
+      for (int k = 0; k < r; ++k) { cudaFree(g_ar.peer[k]); g_ar.peer[k] = nullptr; }
+      return QL_ERR_CUDA;
+    }
+    g_ar.peer[r] = ptr;
+  }
+  if (cudaDeviceSynchronize() != cudaSuccess) { (void)cudaGetLastError(); return QL_ERR_CUDA; }
+  g_ar.local = g_ar.peer[0];
+  g_ar.bytes = max_bytes;
+  g_ar.big_rows = rs_tokens;
+  g_ar.big_hidden = rs_hidden;
+  g_ar.world = world;
+  g_ar.rank = 0;
+  g_ar.emulated = true;
+  g_ar.ready = true;
+  return QL_OK;
+}
+
+int ql_tp_emu_set_rank(int rank) {
+  if (!g_ar.ready || !g_ar.emulated) return QL_ERR_WORKSPACE;
+  if (rank < 0 || rank >= g_ar.world) return QL_ERR_BAD_SHAPE;
+  g_ar.rank = rank;
+  g_ar.local = g_ar.peer[rank];
+  return QL_OK;
+}
+
+// Unmap the peers' areas and free this rank's (after a failed set-up, or at shutdown once every
+// rank has stopped issuing calls).  Idempotent.
+int ql_ar_destroy(void) {
+  if (g_ar.local == nullptr) return QL_OK;
+  (void)cudaDeviceSynchronize();
+  if (g_ar.emulated) {
+    for (int r = 0; r < g_ar.world; ++r)
+      if (g_ar.peer[r] != nullptr) (void)cudaFree(g_ar.peer[r]);
+    (void)cudaGetLastError();
+    g_ar = ArState();
+    return QL_OK;
+  }
+  for (int r = 0; r < g_ar.world; ++r) {
+    if (r != g_ar.rank && g_ar.peer[r] != nullptr) (void)cudaIpcCloseMemHandle(g_ar.peer[r]);
+    g_ar.peer[r] = nullptr;
+  }
+  (void)cudaFree(g_ar.local);
+  (void)cudaGetLastError();
+  g_ar = ArState();
+  return QL_OK;
+}
+
 size_t ql_ar_max_bytes(void) { return g_ar.ready ? g_ar.bytes : 0; }
 
 int ql_ar_allreduce_bf16(const void* in, void* out, int64_t numel, ql_stream_t stream) {
-  if (!g_ar.ready) return QL_ERR_WORKSPACE;
+  if (!g_ar.ready || g_ar.emulated) return QL_ERR_WORKSPACE;
   if (numel < 0 || numel % 8 != 0 || (size_t)numel * 2 > g_ar.bytes) return QL_ERR_BAD_SHAPE;
   if (numel == 0) return QL_OK;
   if (!in || !out) return QL_ERR_NULL;
@@ -212,6 +352,7 @@ int ql_ar_allreduce_bf16(const void* in, void* out, int64_t numel, ql_stream_t s
   p.ctr = reinterpret_cast<uint32_t*>(g_ar.local + ar_ctr_offset(g_ar.bytes, g_ar.world));
   p.nvec = numel / 8;
   p.region = ar_region_bytes(g_ar.bytes);
+  p.timeout_ns = ar_timeout_ns();
   p.world = g_ar.world;
   p.rank = g_ar.rank;
   int64_t blocks = (p.nvec + kArThreads - 1) / kArThreads;
@@ -241,7 +382,7 @@ int ql_ar_rmsnorm_quant(const void* partial, const void* residual_in, void* resi
                         float* s, ql_stream_t stream) {
   if (fmt != QL_INT8 && fmt != QL_FP8_E4M3) return QL_ERR_BAD_FORMAT;
   ArView ar;
-  if (!ar_view(&ar)) return QL_ERR_WORKSPACE;
+  if (!ar_view(&ar) || g_ar.emulated) return QL_ERR_WORKSPACE;
   if (M < 0 || K <= 0 || K % 8 != 0 || (size_t)M * (size_t)K * 2 > ar.max_bytes) return QL_ERR_BAD_SHAPE;
   if (M == 0) return QL_OK;
   if (!partial || !residual_in || !residual_out || !weight || !q || !s) return QL_ERR_NULL;

@@ -199,19 +199,42 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 // Bounded spin for cross-GPU flag waits: a peer that died must not hang this GPU forever.  After
-// ~10 s (globaltimer) the kernel traps, which surfaces as a CUDA error on the host -- loud, not silent.
+// `limit_ns` of %globaltimer (QL_AR_TIMEOUT_S, default 10 s; 0 = wait forever, as NCCL would) the
+// kernel traps, which surfaces as a CUDA error on the host -- loud, not silent.  Legitimate skew
+// (a peer in first-call module load, under a debugger) needs a larger bound or 0.  These kernels
+// cannot run under ncu kernel replay: a replayed launch sees stale epochs and can never match.
 struct SpinGuard {
   uint32_t n = 0;
-  uint64_t t0 = 0;
+  uint64_t t0 = 0, limit;
+  __device__ __forceinline__ explicit SpinGuard(uint64_t limit_ns) : limit(limit_ns) {}
   __device__ __forceinline__ void tick() {
-    if ((++n & 0xfffu) == 0) {
+    if ((++n & 0xfffu) == 0 && limit != 0) {
       uint64_t t;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
       if (t0 == 0) t0 = t;
-      else if (t - t0 > 10000000000ull) __trap();
+      else if (t - t0 > limit) __trap();
     }
   }
 };
+
+// system-scope flag accesses for cross-GPU hand-offs (peer-mapped or local memory)
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// 16-byte load that is never served from a stale L1 line (peer-written or peer-resident data)
+__device__ __forceinline__ uint4 ld_sys128(const void* p) {
+  uint4 r;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
 
 // Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization
 // attribute starts while its predecessor drains; everything that reads the predecessor's output

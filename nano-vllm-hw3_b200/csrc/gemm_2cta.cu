@@ -45,6 +45,15 @@ struct Gemm2Params {
   int group_m;           // token tiles per rasterisation super-group
 };
 
+// Fused reduce-scatter (PUSH): where the tiles go and whom to tell.
+struct Gemm2Push {
+  CUtensorMap ymap[8];        // per token owner: its receive region for THIS rank's partials, [rows_o, N] bf16
+  uint32_t* ready_slot[8];    // ready[this rank] in every rank's flag block (peer-mapped)
+  uint32_t* ctr;              // local {epoch, rows_done, gemm_done, copy_done}
+  int tiles_per_owner;        // 256-token tiles per owner slice
+  int world;
+};
+
 constexpr int kG2Threads = 384;   // 4 control warps + 8 epilogue warps
 constexpr int kG2EpiWarps = 8;
 constexpr int kG2RowsA = 128;    // token rows per CTA (UMMA M = 256 per pair)
@@ -159,11 +168,12 @@ __device__ __forceinline__ void sts32f(uint32_t addr, float v) {
   asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 
-template <int FMT, bool OUT_ACC, bool HAS_BIAS>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kG2Threads, 1)
-gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
-             const __grid_constant__ CUtensorMap tm_y, const Gemm2Params p) {
+template <int FMT, bool OUT_ACC, bool HAS_BIAS, bool PUSH>
+__device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtensorMap& tm_w,
+                                           const CUtensorMap* tm_y, const Gemm2Params& p,
+                                           const Gemm2Push* push) {
   static_assert(!(OUT_ACC && FMT != QL_INT8), "raw accumulators: int8 only");
+  static_assert(!(PUSH && OUT_ACC), "the fused reduce-scatter stores bf16 tiles");
   extern __shared__ uint8_t smem_raw[];
   // all offsets below are identical in both CTAs of the pair (the MMA and the multicast
   // commits address the peer's shared memory by offset)
@@ -184,7 +194,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_x);
     tma_prefetch_desc(&tm_w);
-    tma_prefetch_desc(&tm_y);
+    if constexpr (!PUSH) tma_prefetch_desc(tm_y);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kG2Stages; ++i) {
@@ -312,6 +322,15 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
       const int n0 = tn * kG2TileN + half * 128;                          // first feature of this warp
       const int m0 = tm * 2 * kG2RowsA + (int)cta * kG2RowsA + q * 32;   // first token of this warp
       const int m = m0 + lane;
+      // PUSH: the tile belongs to the rank that owns these 256 tokens; its rows are addressed
+      // relative to the owner's slice, in the owner's receive region for this rank (peer memory)
+      const CUtensorMap* ymap = tm_y;
+      int m_store = m0;
+      if constexpr (PUSH) {
+        const int owner = tm / push->tiles_per_owner;
+        ymap = &push->ymap[owner];
+        m_store = m0 - owner * push->tiles_per_owner * 2 * kG2RowsA;
+      }
       float sxm = 0.0f;
       const uint32_t sw_s = vec0 + acc * (2 * kG2TileN * 4) + half * 128 * 4;
       const uint32_t bias_s = sw_s + kG2TileN * 4;
@@ -391,7 +410,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
           if (lane == 0) {
             // rows >= M and columns >= N are clipped by the TMA unit; a box entirely outside
             // the tensor is not issued
-            if (m0 < p.M && nc < p.N) tma_store_2d(&tm_y, stage_out, nc, m0);
+            if (m0 < p.M && nc < p.N) tma_store_2d(ymap, stage_out, nc, m_store);
             tma_store_commit();
           }
         }
@@ -401,12 +420,46 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
       if (lane == 0) mbar_arrive_cluster(tempty_leader0 + acc * 8);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-    if (lane == 0) tma_store_wait_all();
+    if (lane == 0) {
+      tma_store_wait_all();
+      if constexpr (PUSH) asm volatile("fence.proxy.async.global;" ::: "memory");
+    }
   }
 
   tc_fence_before();
   cluster_sync_all();
   if (warp == 2) tmem_dealloc2(tmem_base, 512);
+  if constexpr (PUSH) {
+    // Every tile of this CTA has landed in its owner's memory (bulk stores waited for above).
+    // The last CTA of the grid raises ready[this rank] = call number on every rank; the owners'
+    // reduce kernels (tp_collective.cu) poll it.  Thread 0 is the TMA producer: it has passed
+    // griddepcontrol.wait, so the call counter it reads is final.
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      if (atomicAdd(push->ctr + 2, 1u) == gridDim.x - 1) {
+        push->ctr[2] = 0;
+        const uint32_t e = *reinterpret_cast<volatile uint32_t*>(push->ctr) + 1;
+        __threadfence_system();
+        for (int r = 0; r < push->world; ++r) st_release_sys(push->ready_slot[r], e);
+      }
+    }
+  }
+}
+
+template <int FMT, bool OUT_ACC, bool HAS_BIAS>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kG2Threads, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+             const __grid_constant__ CUtensorMap tm_y, const Gemm2Params p) {
+  gemm2_body<FMT, OUT_ACC, HAS_BIAS, false>(tm_x, tm_w, &tm_y, p, nullptr);
+}
+
+// GEMM + reduce-scatter over NVLink in one kernel: UTC*MMA tiles whose epilogue TMA-stores into
+// peer memory (see Gemm2Push).
+template <int FMT, bool HAS_BIAS>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kG2Threads, 1)
+gemm2_push_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                  const __grid_constant__ Gemm2Push push, const Gemm2Params p) {
+  gemm2_body<FMT, false, HAS_BIAS, true>(tm_x, tm_w, nullptr, p, &push);
 }
 
 // ------------------------------------------------------------------ host side
@@ -470,6 +523,93 @@ static int launch_g2(const void* qx, const void* qw, void* y, int64_t ldy, Gemm2
     return QL_ERR_CUDA;
   }
   return QL_OK;
+}
+
+static int g2_pairs_max(const void* kern) {
+  static int pairs_max = 0;
+  if (pairs_max == 0) {
+    cudaLaunchConfig_t qc = {};
+    qc.gridDim = dim3(num_sms() & ~1);
+    qc.blockDim = dim3(kG2Threads);
+    qc.dynamicSmemBytes = kG2Smem;
+    int n = 0;   // the kernel carries __cluster_dims__(2, 1, 1)
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &qc) != cudaSuccess || n < 1) {
+      (void)cudaGetLastError();
+      n = num_sms() / 2;
+    }
+    pairs_max = n;
+  }
+  return pairs_max;
+}
+
+template <int FMT, bool HAS_BIAS>
+static int launch_g2_push(const TpView& tp, const void* qx, const void* qw, Gemm2Params p, cudaStream_t st) {
+  auto kern = gemm2_push_kernel<FMT, HAS_BIAS>;
+  static SmemAttrOnce smem_once;
+  if (int e = ensure_max_smem(reinterpret_cast<const void*>(kern), kG2Smem, smem_once)) return e;
+  CUtensorMap tm_x, tm_w;
+  if (!make_tmap_2d(&tm_x, qx, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.M, p.K, kG2BlockK, kG2RowsA) ||
+      !make_tmap_2d(&tm_w, qw, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.N, p.K, kG2BlockK, kG2RowsB))
+    return QL_ERR_CUDA;
+  Gemm2Push push;
+  const int64_t Mo = tp_rows_per_owner(p.M, tp.world);
+  for (int o = 0; o < 8; ++o) {
+    push.ready_slot[o] = nullptr;
+    if (o >= tp.world) { push.ymap[o] = tm_x; continue; }
+    int64_t rows_o = (int64_t)p.M - o * Mo;
+    rows_o = rows_o < 1 ? 1 : (rows_o > Mo ? Mo : rows_o);       // an owner without rows is never addressed
+    uint8_t* base = tp.big[o] + tp.lay.part + (size_t)((int64_t)tp.rank * Mo) * (size_t)p.N * 2;
+    if (!make_tmap_2d(&push.ymap[o], base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p.N, rows_o, (int64_t)p.N * 2,
+                      kG2StoreCols, 32))
+      return QL_ERR_CUDA;
+    push.ready_slot[o] = reinterpret_cast<uint32_t*>(tp.big[o] + tp.lay.flags + kTpReadyOff +
+                                                     (size_t)tp.rank * kTpFlagStride);
+  }
+  push.ctr = reinterpret_cast<uint32_t*>(tp.big[tp.rank] + tp.lay.flags + kTpCtrOff);
+  push.tiles_per_owner = (int)(Mo / (2 * kG2RowsA));
+  push.world = tp.world;
+  p.tiles_m = (p.M + 2 * kG2RowsA - 1) / (2 * kG2RowsA);
+  p.tiles_n = (p.N + kG2TileN - 1) / kG2TileN;
+  {
+    const int64_t g = (48ll << 20) / (256ll * p.K);
+    p.group_m = (int)(g < 1 ? 1 : (g > p.tiles_m ? p.tiles_m : g));
+  }
+  const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+  const int pairs_max = g2_pairs_max(reinterpret_cast<const void*>(kern));
+  const int pairs = (int)(tiles < pairs_max ? tiles : pairs_max);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * pairs));
+  cfg.blockDim = dim3(kG2Threads);
+  cfg.dynamicSmemBytes = kG2Smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  const cudaError_t err = cudaLaunchKernelEx(&cfg, kern, tm_x, tm_w, push, p);
+  count_launch();
+  if (err != cudaSuccess) {
+    (void)cudaGetLastError();
+    return QL_ERR_CUDA;
+  }
+  return QL_OK;
+}
+
+int launch_gemm2_push(const TpView& tp, const void* qx, const float* sx, const void* qw, const float* sw,
+                      const void* bias, int64_t M, int64_t N, int64_t K, int fmt, cudaStream_t st) {
+  if (M == 0 || N == 0) return QL_OK;
+  Gemm2Params p;
+  p.sx = sx; p.sw = sw;
+  p.bias = static_cast<const uint16_t*>(bias);
+  p.acc_out = nullptr;
+  p.M = (int)M; p.N = (int)N; p.K = (int)K;
+  p.tiles_m = p.tiles_n = 0;
+  p.group_m = 1;
+  if (fmt == QL_INT8)
+    return bias ? launch_g2_push<QL_INT8, true>(tp, qx, qw, p, st) : launch_g2_push<QL_INT8, false>(tp, qx, qw, p, st);
+  return bias ? launch_g2_push<QL_FP8_E4M3, true>(tp, qx, qw, p, st)
+              : launch_g2_push<QL_FP8_E4M3, false>(tp, qx, qw, p, st);
 }
 
 bool gemm2_eligible(const void* y, int64_t ldy, const void* sw, const void* bias, bool out_acc) {

@@ -52,18 +52,58 @@ struct ArView {
   uint32_t* ctr;        // local {epoch, done}
   size_t region;        // bytes per (parity, source rank) region
   size_t max_bytes;     // largest payload of one call
+  uint64_t timeout_ns;  // flag-wait bound (0 = forever)
   int world, rank;
 };
 bool ar_view(ArView* v);   // false until ql_ar_open succeeded
+uint64_t ar_timeout_ns();
 int launch_ar_rmsnorm_quant(const ArView& ar, const void* partial, const void* res_in, void* res_out,
                             const void* w, float eps, int64_t M, int64_t K, int fmt, void* q,
                             float* s, cudaStream_t st);
+
+// The "big" section of the symmetric area: the reduce-scatter / all-gather path behind prefill-
+// sized row-parallel linears (tp_collective.cu).  Offsets are relative to a rank's big section.
+struct TpLayout {
+  size_t flags;   // 4 KB: ready[8] (128 B apart) | +1024: done[8] | +2048: {epoch, rows_done, gemm_done, copy_done}
+  size_t part;    // bf16 partial sums: [rows_cap, N] of this rank (pull) or W receive regions (push)
+  size_t q;       // gathered codes  [rows_cap, N] 1 B
+  size_t s;       // gathered scales [rows_cap] fp32
+  size_t y;       // gathered bf16   [rows_cap, N]
+  size_t total;
+};
+struct TpView {
+  uint8_t* big[8];      // every rank's big section as mapped in this process
+  TpLayout lay;
+  size_t rows, rows_cap, hidden;
+  uint64_t timeout_ns;
+  int world, rank;
+  bool emulated;        // all ranks live in this process: one launch runs them all (tests)
+};
+bool tp_view(TpView* v);   // false unless ql_ar_init was given a large-path capacity and ql_ar_open succeeded
+constexpr size_t kTpReadyOff = 0, kTpDoneOff = 1024, kTpCtrOff = 2048, kTpFlagStride = 128;
+// rows per token owner: whole 256-token pair tiles, so that a GEMM tile never straddles two owners
+inline int64_t tp_rows_per_owner(int64_t M, int world) {
+  const int64_t tiles = (M + 255) / 256;
+  return ((tiles + world - 1) / world) * 256;
+}
 
 // CTA-pair (cta_group::2) tcgen05 GEMM for prefill-sized M, per-row scales only.
 int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* sw,
                  const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
                  int64_t K, int fmt, cudaStream_t st);
 bool gemm2_eligible(const void* y, int64_t ldy, const void* sw, const void* bias, bool out_acc);
+// The same kernel as a fused GEMM + reduce-scatter over NVLink: every 256-token output tile is
+// TMA-stored into the receive region of the rank that owns those tokens (peer memory), and the last
+// CTA to finish raises this rank's `ready` flag on every peer.  M rows in total, owner slices of
+// tp_rows_per_owner(M, world) rows.
+int launch_gemm2_push(const TpView& tp, const void* qx, const float* sx, const void* qw, const float* sw,
+                      const void* bias, int64_t M, int64_t N, int64_t K, int fmt, cudaStream_t st);
+// Reduce (fp32, rank order) the W partials of this rank's token slice, round to bf16, then either
+// quantise per token and all-gather codes + scales (fmt = QL_INT8 / QL_FP8_E4M3) or all-gather the
+// bf16 rows and copy the full result to `out` (fmt < 0).  `pushed`: partials were delivered by
+// launch_gemm2_push; otherwise every rank's partial sits in its own `part` buffer and is pulled.
+int launch_tp_reduce(const TpView& tp, int64_t M, int64_t N, int fmt, int pushed, void* out, int64_t ldo,
+                     cudaStream_t st);
 // Which GEMM kernel launch_gemm picks: 1 = single-CTA weight-stationary, 2 = CTA pair.
 int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group);
 

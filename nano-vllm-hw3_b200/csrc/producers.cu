@@ -382,6 +382,7 @@ struct ArArgs {
   uint8_t* area[8];
   uint32_t* ctr;
   size_t region;
+  uint64_t timeout_ns;
   int rank;
 };
 
@@ -452,7 +453,7 @@ ar_rmsnorm_quant_kernel(const ArArgs ar, const uint16_t* __restrict__ partial, c
         const uint8_t* src = ar.area[ar.rank] + par + (size_t)r * ar.region +
                              (size_t)(rowc * nvec + idx) * 32;
         uint4 a, b;
-        SpinGuard guard;
+        SpinGuard guard(ar.timeout_ns);
         while (true) { a = ar_ld_packet(src); if (a.y == e && a.w == e) break; guard.tick(); }
         while (true) { b = ar_ld_packet(src + 16); if (b.y == e && b.w == e) break; guard.tick(); }
         v = make_uint4(a.x, a.z, b.x, b.z);
@@ -659,6 +660,7 @@ int launch_ar_rmsnorm_quant(const ArView& ar, const void* partial, const void* r
   for (int r = 0; r < 8; ++r) a.area[r] = ar.area[r];
   a.ctr = ar.ctr;
   a.region = ar.region;
+  a.timeout_ns = ar.timeout_ns;
   a.rank = ar.rank;
   const auto* pp = static_cast<const uint16_t*>(partial);
   const auto* rp = static_cast<const uint16_t*>(res_in);

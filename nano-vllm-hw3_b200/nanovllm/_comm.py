@@ -1,11 +1,24 @@
-"""Host side of the one-shot NVLink all-reduce (csrc/allreduce.cu, C ABI ``ql_ar_*``).
+"""Host side of the NVLink peer-memory collectives behind the row-parallel linears
+(csrc/allreduce.cu, csrc/tp_collective.cu, csrc/gemm_2cta.cu; C ABI ``ql_ar_*`` / ``ql_tp_*``).
 
-Used by ``RowParallelLinear.forward`` in place of ``dist.all_reduce(y)`` (reference
-nanovllm/layers/linear.py:150-152) when the bf16 output is small (decode-sized
-batches, where NCCL's launch + protocol latency exceeds the GEMM).  ``torch.distributed`` is only
-the plumbing: it carries the CUDA IPC handles once at start-up.  Larger outputs stay on NCCL.
+Two regimes replace ``dist.all_reduce(y)`` of ``RowParallelLinear.forward`` (reference
+nanovllm/layers/linear.py:150-152):
 
-``QL_PEER_AR=0`` disables it; ``QL_PEER_AR_BYTES`` sets the buffer size (default 1 MiB of payload).
+* decode-sized outputs (<= ``QL_PEER_AR_BYTES``, default 1 MiB): the one-shot push all-reduce
+  (``ql_ar_allreduce_bf16``), optionally fused with add + RMSNorm + quant (``ql_ar_rmsnorm_quant``);
+* prefill-sized outputs (<= ``QL_TP_TOKENS`` x ``QL_TP_HIDDEN``, default 65536 x 4096): reduce-scatter
+  to the token owner -- pushed from the GEMM epilogue (``ql_tp_gemm_push``) or pulled by the owner --
+  then the per-token quantiser on the owner's tokens only and an all-gather of codes + scales
+  (``ql_tp_reduce_quant_gather``), or of bf16 rows (``ql_tp_allreduce_bf16``).
+
+``torch.distributed`` is only the plumbing: it carries the CUDA IPC handles once at start-up and
+agrees on success.  Set-up is collective and failure-tolerant: every stage's status is MIN-reduced
+over the ranks, and if any rank fails (no peer access between a GPU pair, cudaIpcOpenMemHandle
+refused, out of memory, different sizes per rank) every rank frees what it mapped and returns
+``None`` -- the layers then keep using NCCL.  Anything larger than the buffers stays on NCCL too.
+
+``QL_PEER_AR=0`` disables everything here; ``QL_TP_BIG=0`` only the prefill-sized path;
+``QL_TP_PUSH=0`` makes the owners pull the partials instead of the GEMM pushing them.
 """
 from __future__ import annotations
 
@@ -20,22 +33,74 @@ from nanovllm import _ext
 _state = {"tried": False, "comm": None}
 
 
+class _DevMem:
+    """A window of the symmetric area as something ``torch.as_tensor`` can wrap (zero copy)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+def _all_ok(ok: bool) -> bool:
+    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t.item())
+
+
 class PeerAllReduce:
 
-    def __init__(self, max_bytes: int):
+    def __init__(self, lib, world: int, rank: int):
+        self.lib, self.world, self.rank = lib, world, rank
+        self.bytes = int(lib.ql_ar_max_bytes())
+        self.tp_tokens = int(lib.ql_tp_max_tokens())
+        self.tp_hidden = int(lib.ql_tp_max_hidden())
+        self.push = os.environ.get("QL_TP_PUSH", "1") != "0"
+        self._bufs = {}
+        if self.tp_tokens:
+            dev = torch.device("cuda", torch.cuda.current_device())
+            cap = self.tp_tokens * self.tp_hidden
+            for which, nbytes in ((0, cap * 2), (1, cap), (2, self.tp_tokens * 4)):
+                ptr = lib.ql_tp_buffer(which)
+                self._bufs[which] = torch.as_tensor(_DevMem(ptr, nbytes), device=dev)
+
+    @classmethod
+    def create(cls, max_bytes: int, tp_tokens: int, tp_hidden: int) -> "PeerAllReduce | None":
+        """Collective constructor.  Returns None on EVERY rank if any rank cannot set it up."""
         lib = _ext.load()
-        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        world, rank = dist.get_world_size(), dist.get_rank()
+        # every rank must ask for the same area, or remote offsets would be wrong
+        sizes = [None] * world
+        dist.all_gather_object(sizes, (max_bytes, tp_tokens, tp_hidden))
+        if len(set(sizes)) != 1:
+            return None
+        if not _all_ok(lib.ql_ar_can_access_peers(world) == 0):
+            return None
         hb = lib.ql_ar_handle_bytes()
         mine = ctypes.create_string_buffer(hb)
-        _ext._check(lib.ql_ar_init(max_bytes, self.world, self.rank, mine))
-        handles = [None] * self.world
+        ok = lib.ql_ar_init(max_bytes, tp_tokens, tp_hidden, world, rank, mine) == 0
+        if not _all_ok(ok):
+            lib.ql_ar_destroy()
+            return None
+        handles = [None] * world
         dist.all_gather_object(handles, mine.raw)
-        blob = ctypes.create_string_buffer(b"".join(handles), hb * self.world)
-        _ext._check(lib.ql_ar_open(blob))
-        self.bytes = int(lib.ql_ar_max_bytes())
+        blob = ctypes.create_string_buffer(b"".join(handles), hb * world)
+        ok = lib.ql_ar_open(blob) == 0
+        if not _all_ok(ok):
+            lib.ql_ar_destroy()
+            return None
         torch.cuda.synchronize()
         dist.barrier()                       # every peer has mapped every area before first use
+        return cls(lib, world, rank)
 
+    def close(self) -> None:
+        """Collective: unmap and free (no rank may have a call in flight)."""
+        torch.cuda.synchronize()
+        dist.barrier()
+        self._bufs = {}
+        self.lib.ql_ar_destroy()
+        _state["comm"] = None
+
+    # ------------------------------------------------------------------ decode-sized: one shot
     def fits(self, numel: int) -> bool:
         return numel % 8 == 0 and 0 < numel * 2 <= self.bytes
 
@@ -44,10 +109,9 @@ class PeerAllReduce:
         """Sum of every rank's y (fp32, rank order, one rounding) -> fresh bf16 tensor."""
         assert y.dtype == torch.bfloat16 and y.is_contiguous() and self.fits(y.numel())
         out = torch.empty_like(y)
-        _ext._check(_ext.load().ql_ar_allreduce_bf16(y.data_ptr(), out.data_ptr(), y.numel(),
-                                                     torch.cuda.current_stream().cuda_stream))
+        _ext._check(self.lib.ql_ar_allreduce_bf16(y.data_ptr(), out.data_ptr(), y.numel(),
+                                                  torch.cuda.current_stream().cuda_stream))
         return out
-
 
     def fits_fused(self, M: int, K: int) -> bool:
         return K % 8 == 0 and K <= 8192 and 0 < M * K * 2 <= self.bytes
@@ -61,15 +125,56 @@ class PeerAllReduce:
         q = torch.empty((M, K), dtype=dtype, device=partial.device)
         s = torch.empty((M,), dtype=torch.float32, device=partial.device)
         res = torch.empty_like(residual)
-        _ext._check(_ext.load().ql_ar_rmsnorm_quant(
+        _ext._check(self.lib.ql_ar_rmsnorm_quant(
             partial.data_ptr(), residual.data_ptr(), res.data_ptr(), weight.data_ptr(), float(eps), M, K,
             _ext.fmt_of(dtype), q.data_ptr(), s.data_ptr(), torch.cuda.current_stream().cuda_stream))
         return q, s, res
 
+    # ------------------------------------------------------------------ prefill-sized: reduce-scatter
+    def fits_big(self, M: int, N: int) -> bool:
+        # token owners hold whole 256-token tiles; the buffers carry that rounding (allreduce.cu)
+        return bool(self.tp_tokens) and 0 < M <= self.tp_tokens and N % 8 == 0 and 0 < N <= self.tp_hidden
+
+    def partial_view(self, M: int, N: int) -> torch.Tensor:
+        """bf16 [M, N] window of this rank's partial buffer: where a row-parallel GEMM writes when
+        the owners pull."""
+        return self._bufs[0][: M * N * 2].view(torch.bfloat16).view(M, N)
+
+    @torch.no_grad()
+    def gemm_push(self, qx, sx, qw, sw, bias, dtype) -> None:
+        """ql_tp_gemm_push: row-parallel W8A8 GEMM whose epilogue delivers every 256-token tile to
+        the rank that owns those tokens (GEMM + reduce-scatter in one kernel)."""
+        assert qx.dtype == dtype and qw.dtype == dtype and qx.is_contiguous() and qw.is_contiguous()
+        M, K = qx.shape
+        N = qw.shape[0]
+        assert K % 128 == 0 and self.fits_big(M, N)
+        _ext._check(self.lib.ql_tp_gemm_push(qx.data_ptr(), sx.data_ptr(), qw.data_ptr(), sw.data_ptr(),
+                                             None if bias is None else bias.data_ptr(), M, N, K,
+                                             _ext.fmt_of(dtype), torch.cuda.current_stream().cuda_stream))
+
+    @torch.no_grad()
+    def reduce_quant_gather(self, M: int, N: int, dtype, pushed: bool):
+        """ql_tp_reduce_quant_gather -> (q [M, N], s [M]): views of the symmetric buffers, valid
+        until the next prefill-sized collective."""
+        _ext._check(self.lib.ql_tp_reduce_quant_gather(M, N, _ext.fmt_of(dtype), 1 if pushed else 0,
+                                                       torch.cuda.current_stream().cuda_stream))
+        q = self._bufs[1][: M * N].view(dtype).view(M, N)
+        s = self._bufs[2][: M * 4].view(torch.float32)
+        return q, s
+
+    @torch.no_grad()
+    def all_reduce_big(self, M: int, N: int, pushed: bool, device) -> torch.Tensor:
+        """ql_tp_allreduce_bf16 -> fresh bf16 [M, N] (dist.all_reduce semantics)."""
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=device)
+        _ext._check(self.lib.ql_tp_allreduce_bf16(M, N, 1 if pushed else 0, out.data_ptr(), N,
+                                                  torch.cuda.current_stream().cuda_stream))
+        return out
+
 
 def get() -> PeerAllReduce | None:
     """The process-wide communicator, created on first use (never during CUDA-graph capture:
-    callers run one eager forward first, as the engine's warm-up does, model_runner.py:91-103)."""
+    callers run one eager forward first, as the engine's warm-up does, model_runner.py:91-103).
+    Creation is collective: every rank reaches it at the same point of its first forward."""
     if _state["tried"]:
         return _state["comm"]
     if torch.cuda.is_available() and torch.cuda.is_current_stream_capturing():
@@ -81,5 +186,12 @@ def get() -> PeerAllReduce | None:
         return None
     if dist.get_backend() != "nccl" or dist.get_world_size() not in (2, 4, 8):
         return None
-    _state["comm"] = PeerAllReduce(int(os.environ.get("QL_PEER_AR_BYTES", str(1 << 20))))
+    big = os.environ.get("QL_TP_BIG", "1") != "0"
+    tokens = int(os.environ.get("QL_TP_TOKENS", str(65536))) if big else 0
+    hidden = int(os.environ.get("QL_TP_HIDDEN", str(4096))) if big else 0
+    try:
+        _state["comm"] = PeerAllReduce.create(int(os.environ.get("QL_PEER_AR_BYTES", str(1 << 20))),
+                                              tokens, hidden)
+    except Exception:                        # noqa: BLE001 -- a collective in create() failed: NCCL from here on
+        _state["comm"] = None
     return _state["comm"]

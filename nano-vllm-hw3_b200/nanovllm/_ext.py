@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libqlinear_b200.so")
 
 QL_INT8, QL_FP8_E4M3 = 0, 1
-QL_ABI_VERSION = 5
+QL_ABI_VERSION = 6
 _FMT = {torch.int8: QL_INT8, torch.float8_e4m3fn: QL_FP8_E4M3}
 
 _c_i64, _c_int, _c_vp, _c_sz = ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
@@ -45,12 +45,22 @@ SIGNATURES = {
                                   _c_int, _c_vp, _c_vp, _c_vp, _c_vp]),
     "ql_silu_mul_quant": (_c_int, [_c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp, _c_vp, _c_vp, _c_vp]),
     "ql_ar_handle_bytes": (_c_sz, []),
-    "ql_ar_init": (_c_int, [_c_sz, _c_int, _c_int, _c_vp]),
+    "ql_ar_can_access_peers": (_c_int, [_c_int]),
+    "ql_ar_init": (_c_int, [_c_sz, _c_sz, _c_sz, _c_int, _c_int, _c_vp]),
     "ql_ar_open": (_c_int, [_c_vp]),
+    "ql_ar_destroy": (_c_int, []),
     "ql_ar_max_bytes": (_c_sz, []),
     "ql_ar_allreduce_bf16": (_c_int, [_c_vp, _c_vp, _c_i64, _c_vp]),
     "ql_ar_rmsnorm_quant": (_c_int, [_c_vp, _c_vp, _c_vp, _c_vp, ctypes.c_float, _c_i64, _c_i64, _c_int,
                                      _c_vp, _c_vp, _c_vp]),
+    "ql_ar_init_local": (_c_int, [_c_sz, _c_sz, _c_sz, _c_int]),
+    "ql_tp_emu_set_rank": (_c_int, [_c_int]),
+    "ql_tp_max_tokens": (_c_sz, []),
+    "ql_tp_max_hidden": (_c_sz, []),
+    "ql_tp_buffer": (_c_vp, [_c_int]),
+    "ql_tp_gemm_push": (_c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64, _c_int, _c_vp]),
+    "ql_tp_reduce_quant_gather": (_c_int, [_c_i64, _c_i64, _c_int, _c_int, _c_vp]),
+    "ql_tp_allreduce_bf16": (_c_int, [_c_i64, _c_i64, _c_int, _c_vp, _c_i64, _c_vp]),
     "ql_workspace_bytes": (_c_sz, [_c_i64, _c_i64]),
     "ql_linear_path": (ctypes.c_char_p, [_c_i64, _c_i64, _c_i64, _c_i64]),
 }

@@ -188,18 +188,72 @@ class RowParallelLinear(LinearBase):
         all-reduce + RMSNorm + quant (`RMSNorm.forward_quant(..., partial=True)`)."""
         return self._linear(x, self.bias if self.tp_rank == 0 else None)
 
+    def _comm(self):
+        if self.tp_size == 1 or self.qw is None:
+            return None
+        from nanovllm import _comm
+        return _comm.get()
+
+    def _big_partial(self, comm, x, bias):
+        """Prefill-sized output: leave this rank's partial sums where the token owners can reduce
+        them.  Returns (M, N, pushed).  Per-row scales: the CTA-pair GEMM pushes every 256-token
+        tile into its owner's receive region from its epilogue (GEMM + reduce-scatter in one
+        kernel); otherwise (per-group scales, QL_TP_PUSH=0) the GEMM writes into this rank's
+        window of the symmetric area and the owners pull."""
+        b = None if bias is None else bias.data
+        N = self.qw.shape[0]
+        if comm.push and self.group_size == 0:
+            if hasattr(x, "q") and hasattr(x, "s"):
+                qx, sx = x.q, x.s
+            else:
+                qx, sx = _ext.quant_rows(x.reshape(-1, x.shape[-1]), self.qdtype)
+            comm.gemm_push(qx, sx, self.qw, self._sw_kernel, b, self.qdtype)
+            return qx.shape[0], N, True
+        M = x.q.shape[0] if hasattr(x, "q") else x.reshape(-1, x.shape[-1]).shape[0]
+        self._linear(x, bias, out=comm.partial_view(M, N))
+        return M, N, False
+
+    def forward_quant(self, x):
+        """Row-parallel linear whose all-reduced output is handed to the NEXT quantized linear
+        already quantised per token (``QuantizedActivation``): under tensor parallelism the
+        reduction is a reduce-scatter to the token owner, the owner quantises its tokens only, and
+        codes + scales are all-gathered -- instead of `dist.all_reduce` (linear.py:150-152)
+        followed by `per_row_quant` over all tokens on every rank (utils/quantization.py:323).
+        Bit-identical to all-reduce (fp32, rank order) + per_row_quant."""
+        from nanovllm.layers.layernorm import QuantizedActivation
+        assert self.qw is not None, "forward_quant needs a quantized layer"
+        bias = self.bias if self.tp_rank == 0 else None
+        comm = self._comm()
+        M = x.q.shape[0] if hasattr(x, "q") else x.reshape(-1, x.shape[-1]).shape[0]
+        N = self.qw.shape[0]
+        if comm is not None and comm.fits_big(M, N) and not comm.fits(M * N):
+            M, N, pushed = self._big_partial(comm, x, bias)
+            return QuantizedActivation(*comm.reduce_quant_gather(M, N, self.qdtype, pushed))
+        y = self.forward(x)
+        return QuantizedActivation(*_ext.quant_rows(y.reshape(-1, N), self.qdtype))
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         bias = self.bias if self.tp_rank == 0 else None
-        y = self._linear(x, bias)
-        if self.tp_size > 1:
-            comm = None
-            if self.qw is not None:
-                from nanovllm import _comm
-                comm = _comm.get()
-            if comm is not None and y.is_contiguous() and comm.fits(y.numel()):
+        if self.tp_size == 1:
+            return self._linear(x, bias)
+        comm = self._comm()
+        if comm is not None:
+            M = x.q.shape[0] if hasattr(x, "q") else x.reshape(-1, x.shape[-1]).shape[0]
+            N = self.qw.shape[0]
+            lead = list(x.q.shape[:-1] if hasattr(x, "q") else x.shape[:-1])
+            if comm.fits(M * N):
                 # decode-sized output: one push-protocol kernel over NVLink peer memory
                 # (csrc/allreduce.cu) instead of the NCCL call
-                y = comm.all_reduce(y)
-            else:
-                dist.all_reduce(y)                       # reference linear.py:150-152
+                y = self._linear(x, bias)
+                if y.is_contiguous():
+                    return comm.all_reduce(y)
+                dist.all_reduce(y)
+                return y
+            if comm.fits_big(M, N):
+                # prefill-sized output: reduce-scatter (from the GEMM epilogue) + all-gather
+                M, N, pushed = self._big_partial(comm, x, bias)
+                dev = x.q.device if hasattr(x, "q") else x.device
+                return comm.all_reduce_big(M, N, pushed, dev).view(lead + [N])
+        y = self._linear(x, bias)
+        dist.all_reduce(y)                               # reference linear.py:150-152
         return y

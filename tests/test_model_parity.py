@@ -10,7 +10,8 @@ oracle (``OracleLinear``), so every difference in the logits is the quantized-li
 
 Bars (north_star: "bit-exact int32 accumulators for INT8 ... unchanged test_ppl.py perplexity
 within 0.5%"; no Qwen3 weights / WikiText-2 exist offline, so the corpus is drawn from the bf16
-teacher's own next-token distribution, see tiny_qwen3.synthetic_corpus):
+teacher's own next-token distribution and the perplexity is taken in expectation over that
+corpus -- tiny_qwen3.pseudo_ppl; the single-sample value is recorded next to it):
 
   INT8 per-row ............ logits BIT-EQUAL to the restated reference chain (every dispatch
                             branch that lands on it, TP-in-place and foreign-wrapped, fused
@@ -74,7 +75,8 @@ def corpus(ext):
     teacher = tq.TinyQwen3ForCausalLM(LAYERS, VOCAB, tq.tp_linears)
     logits = teacher(_ids())
     targets = tq.synthetic_corpus(logits)
-    return {"teacher_logits": logits.cpu(), "targets": targets, "ppl": tq.pseudo_ppl(logits, targets)}
+    return {"teacher_logits": logits.cpu(), "targets": targets, "ppl": tq.pseudo_ppl(logits, logits),
+            "ppl_sampled": tq.pseudo_ppl_sampled(logits, targets)}
 
 
 def _engine(factory, dtype, quant_type, group_size=128):
@@ -121,9 +123,10 @@ def test_int8_per_row_logits_bit_equal(ext, corpus, factory, quant_type):
     assert ext.launch_count() > n0, "the CUDA path did not run"
     ref = _oracle(torch.int8, quant_type, "reference")(ids)
     assert torch.equal(logits, ref), f"max |d logit| = {(logits - ref).abs().max().item()}"
-    ppl = tq.pseudo_ppl(logits, corpus["targets"])
+    ppl = tq.pseudo_ppl(logits, corpus["teacher_logits"])
     _RESULTS[f"int8/per_row/{factory}/{quant_type}"] = {
-        "ppl": ppl, "ppl_reference_chain": tq.pseudo_ppl(ref, corpus["targets"]),
+        "ppl": ppl, "ppl_reference_chain": tq.pseudo_ppl(ref, corpus["teacher_logits"]),
+        "ppl_sampled": tq.pseudo_ppl_sampled(logits, corpus["targets"]),
         "ppl_bf16_teacher": corpus["ppl"], "logits_bit_equal": True}
 
 
@@ -164,16 +167,18 @@ def test_pseudo_ppl_within_bar(ext, corpus, factory, dtype_name, quant_type):
         assert all(isinstance(layer.mlp.down_proj, want) for layer in m.model.layers)
     ids = _ids()
     logits = m(ids)
-    tg = corpus["targets"]
-    ppl = tq.pseudo_ppl(logits, tg)
+    tl, tg = corpus["teacher_logits"], corpus["targets"]
+    ppl = tq.pseudo_ppl(logits, tl)
     same = _oracle(dtype, quant_type, "w8a8")(ids)            # same semantics, restated on the CPU
-    ppl_same = tq.pseudo_ppl(same, tg)
+    ppl_same = tq.pseudo_ppl(same, tl)
     rec = {"ppl": ppl, "ppl_oracle_w8a8": ppl_same, "ppl_bf16_teacher": corpus["ppl"],
-           "ppl_vs_oracle_w8a8": ppl / ppl_same - 1.0, "logits_rel_l2_vs_oracle_w8a8": _rel_l2(logits, same)}
+           "ppl_vs_oracle_w8a8": ppl / ppl_same - 1.0, "logits_rel_l2_vs_oracle_w8a8": _rel_l2(logits, same),
+           "ppl_sampled": tq.pseudo_ppl_sampled(logits, tg),
+           "ppl_sampled_oracle_w8a8": tq.pseudo_ppl_sampled(same, tg)}
     assert abs(ppl / ppl_same - 1.0) <= PPL_TOL, rec
     if quant_type != "per_row":
         ref = _oracle(dtype, quant_type, "reference")(ids)    # the reference's weight-only semantics
-        ppl_ref = tq.pseudo_ppl(ref, tg)
+        ppl_ref = tq.pseudo_ppl(ref, tl)
         rec.update(ppl_reference_weight_only=ppl_ref, ppl_vs_reference_weight_only=ppl / ppl_ref - 1.0,
                    logits_rel_l2_vs_reference_weight_only=_rel_l2(logits, ref))
         assert abs(ppl / ppl_ref - 1.0) <= W8A8_VS_WEIGHT_ONLY_TOL, rec

@@ -32,7 +32,9 @@ def _worker(rank, world, port, q):
             if p_ not in sys.path:
                 sys.path.insert(0, p_)
         import torch.distributed as dist
-        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        # QL_TP_BIG=0: this file is about the one-shot (decode-sized) kernels; outputs beyond their
+        # buffer must take NCCL here (the prefill-sized path has tests/test_tp_collective.py)
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), QL_TP_BIG="0")
         torch.cuda.set_device(rank)
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
         from nanovllm import _comm, _ext
