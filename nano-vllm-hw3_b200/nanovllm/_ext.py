@@ -97,7 +97,28 @@ def fmt_of(dtype: torch.dtype) -> int:
 
 
 def _stream(t: torch.Tensor) -> int:
-    return torch.cuda.current_stream(t.device).cuda_stream
+    return torch._C._cuda_getCurrentRawStream(t.device.index)
+
+
+class _on_device:
+    """``with torch.cuda.device(t.device)`` without its cost when the device is already current
+    (the engine runs one process per GPU, model_runner.py:29)."""
+
+    __slots__ = ("index", "prev")
+
+    def __init__(self, t: torch.Tensor):
+        self.index = t.device.index
+
+    def __enter__(self):
+        cur = torch.cuda.current_device()
+        self.prev = cur if cur != self.index else -1
+        if self.prev >= 0:
+            torch.cuda.set_device(self.index)
+
+    def __exit__(self, *exc):
+        if self.prev >= 0:
+            torch.cuda.set_device(self.prev)
+        return False
 
 
 def _ptr(t):
@@ -122,7 +143,7 @@ def quant_rows(x: torch.Tensor, dtype: torch.dtype):
     M, K = x.shape
     q = torch.empty((M, K), dtype=dtype, device=x.device)
     s = torch.empty((M,), dtype=torch.float32, device=x.device)
-    with torch.cuda.device(x.device):
+    with _on_device(x):
         _check(load().ql_quant_rows(_ptr(x), M, K, x.stride(0) if M > 1 else K, fmt, _ptr(q),
                                     _ptr(s), _stream(x)))
     return q, s
@@ -141,7 +162,7 @@ def quant_groups(w: torch.Tensor, group_size: int, dtype: torch.dtype):
     N, K = w.shape
     q = torch.empty((N, K), dtype=dtype, device=w.device)
     s = torch.empty((N, K // group_size), dtype=torch.float32, device=w.device)
-    with torch.cuda.device(w.device):
+    with _on_device(w):
         _check(load().ql_quant_groups(_ptr(w), N, K, group_size, fmt, _ptr(q), _ptr(s), _stream(w)))
     return q, s
 
@@ -156,7 +177,7 @@ def quant_tensor(x: torch.Tensor, dtype: torch.dtype):
     q = torch.empty(x.shape, dtype=dtype, device=x.device)
     scale = torch.empty((), dtype=torch.bfloat16, device=x.device)
     ws = torch.empty((1024,), dtype=torch.float32, device=x.device)
-    with torch.cuda.device(x.device):
+    with _on_device(x):
         _check(load().ql_quant_tensor(_ptr(x), x.numel(), fmt, _ptr(q), _ptr(scale), _ptr(ws),
                                       ws.numel() * 4, _stream(x)))
     return q, scale
@@ -177,11 +198,44 @@ def _prep_linear(x, qw, sw, bias, group_size):
         assert sw.numel() == N
     if bias is not None:
         assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
-    y_shape = list(x.shape[:-1]) + [N]
-    x2 = x.reshape(-1, K)                                    # reference :322 (view when possible)
+    if x.dim() == 2:                                         # the engine's token-major activations
+        x2, y_shape = x, None
+    else:
+        y_shape = list(x.shape[:-1]) + [N]
+        x2 = x.reshape(-1, K)                                # reference :322 (view when possible)
     if x2.stride(-1) != 1 or (x2.shape[0] > 1 and x2.stride(0) % 8 != 0) or x2.data_ptr() % 16:
         x2 = x2.contiguous()
     return x2, y_shape, N, K
+
+
+# One scratch buffer per (device, stream) instead of a torch.empty per call: every use is ordered
+# on that stream (the next call's quantiser starts behind griddepcontrol.wait, i.e. after the GEMM
+# that read the buffer has finished).  Buffers only grow and outgrown ones are kept alive, so a
+# pointer handed to a kernel never dangles.  During CUDA-graph capture the scratch comes from
+# the graph's own pool instead (graphs captured on one stream may be replayed concurrently).
+_WS, _WS_KEEP = {}, []
+
+
+def _raw_stream(index: int) -> int:
+    return torch._C._cuda_getCurrentRawStream(index)
+
+
+def _workspace(dev, index: int, stream: int, nbytes: int):
+    if torch.cuda.is_current_stream_capturing():
+        return torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+    key = (index, stream)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() < nbytes:
+        if ws is not None:
+            _WS_KEEP.append(ws)
+        ws = torch.empty((max(nbytes, 1 << 20),), dtype=torch.uint8, device=dev)
+        _WS[key] = ws
+    return ws
+
+
+def workspace_bytes(M: int, K: int) -> int:
+    """ql_workspace_bytes, mirrored (qx [M,K] rounded to 256 B + sx [M] rounded to 256 B)."""
+    return ((M * K + 255) // 256 + (M * 4 + 255) // 256) * 256 if M > 0 and K > 0 else 0
 
 
 @torch.no_grad()
@@ -191,15 +245,28 @@ def linear(x, qw, sw, bias, dtype, group_size: int = 0, out: torch.Tensor | None
     assert qw.dtype == dtype
     x2, y_shape, N, K = _prep_linear(x, qw, sw, bias, group_size)
     M = x2.shape[0]
-    y = out if out is not None else torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    dev = x2.device
+    index = dev.index
+    y = out if out is not None else torch.empty((M, N), dtype=torch.bfloat16, device=dev)
     lib = load()
-    nbytes = lib.ql_workspace_bytes(M, K)
-    ws = torch.empty((nbytes,), dtype=torch.uint8, device=x.device) if nbytes else None
-    with torch.cuda.device(x.device):
-        _check(lib.ql_linear(_ptr(x2), x2.stride(0) if M > 1 else K, _ptr(qw), _ptr(sw), _ptr(bias),
-                             _ptr(y), y.stride(0) if M > 1 else N, M, N, K, fmt, group_size,
-                             _ptr(ws), nbytes, _stream(x)))
-    return y.view(y_shape) if out is None else out
+    switch = index != torch.cuda.current_device()
+    if switch:
+        prev = torch.cuda.current_device()
+        torch.cuda.set_device(index)
+    try:
+        stream = _raw_stream(index)
+        nbytes = workspace_bytes(M, K)
+        ws = _workspace(dev, index, stream, nbytes) if nbytes else None
+        _check(lib.ql_linear(x2.data_ptr(), x2.stride(0) if M > 1 else K, qw.data_ptr(), sw.data_ptr(),
+                             None if bias is None else bias.data_ptr(), y.data_ptr(),
+                             y.stride(0) if M > 1 else N, M, N, K, fmt, group_size,
+                             None if ws is None else ws.data_ptr(), nbytes, stream))
+    finally:
+        if switch:
+            torch.cuda.set_device(prev)
+    if out is not None:
+        return out
+    return y if y_shape is None else y.view(y_shape)
 
 
 @torch.no_grad()
@@ -211,7 +278,7 @@ def gemm_w8a8(qx, sx, qw, sw, bias, dtype, group_size: int = 0, out: torch.Tenso
     N = qw.shape[0]
     assert K % 128 == 0, f"K({K}) must be multiple of BLK_K(128)"
     y = out if out is not None else torch.empty((M, N), dtype=torch.bfloat16, device=qx.device)
-    with torch.cuda.device(qx.device):
+    with _on_device(qx):
         _check(load().ql_gemm_w8a8(_ptr(qx), _ptr(sx), _ptr(qw), _ptr(sw), _ptr(bias), _ptr(y), N,
                                    M, N, K, fmt, group_size, _stream(qx)))
     return y
@@ -226,7 +293,7 @@ def gemm_i8_acc(qx, qw):
     N = qw.shape[0]
     assert K % 128 == 0
     acc = torch.empty((M, N), dtype=torch.int32, device=qx.device)
-    with torch.cuda.device(qx.device):
+    with _on_device(qx):
         _check(load().ql_gemm_i8_acc(_ptr(qx), _ptr(qw), _ptr(acc), M, N, K, _stream(qx)))
     return acc
 
@@ -238,7 +305,7 @@ def gemv_w8a8(x, qw, sw, bias, dtype, group_size: int = 0):
     x2, y_shape, N, K = _prep_linear(x, qw, sw, bias, group_size)
     M = x2.shape[0]
     y = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
-    with torch.cuda.device(x.device):
+    with _on_device(x):
         _check(load().ql_gemv_w8a8(_ptr(x2), x2.stride(0) if M > 1 else K, _ptr(qw), _ptr(sw),
                                    _ptr(bias), _ptr(y), N, M, N, K, fmt, group_size, _stream(x)))
     return y.view(y_shape)
@@ -267,7 +334,7 @@ def rmsnorm_quant(x, weight, eps: float, residual=None, dtype=None, want_bf16: b
     q = torch.empty((M, K), dtype=dtype, device=x.device) if dtype is not None else None
     s = torch.empty((M,), dtype=torch.float32, device=x.device) if dtype is not None else None
     h = torch.empty((M, K), dtype=torch.bfloat16, device=x.device) if (want_bf16 or dtype is None) else None
-    with torch.cuda.device(x.device):
+    with _on_device(x):
         _check(load().ql_rmsnorm_quant(_ptr(x), x.stride(0) if M > 1 else K, _ptr(residual), _ptr(residual_out),
                                        _ptr(weight), float(eps), M, K, fmt, _ptr(q), _ptr(s), _ptr(h),
                                        _stream(x)))
@@ -284,7 +351,7 @@ def silu_mul_quant(gate_up, dtype=None, want_bf16: bool = False):
     q = torch.empty((M, I), dtype=dtype, device=gate_up.device) if dtype is not None else None
     s = torch.empty((M,), dtype=torch.float32, device=gate_up.device) if dtype is not None else None
     h = torch.empty((M, I), dtype=torch.bfloat16, device=gate_up.device) if (want_bf16 or dtype is None) else None
-    with torch.cuda.device(gate_up.device):
+    with _on_device(gate_up):
         _check(load().ql_silu_mul_quant(_ptr(gate_up), gate_up.stride(0) if M > 1 else 2 * I, M, I, fmt,
                                         _ptr(q), _ptr(s), _ptr(h), _stream(gate_up)))
     return q, s, h

@@ -75,6 +75,12 @@ def test_workspace_bytes(lib):
     assert lib.ql_workspace_bytes(4096, 3072) >= 4096 * 3072 + 4096 * 4
 
 
+def test_python_workspace_size_mirrors_the_library(lib):
+    from nanovllm import _ext
+    for M, K in [(0, 1024), (1, 128), (16, 4096), (17, 1024), (4096, 3072), (33, 12288), (8192, 1024)]:
+        assert _ext.workspace_bytes(M, K) == lib.ql_workspace_bytes(M, K), (M, K)
+
+
 def test_validation_precedes_device_work(lib):
     """Bad arguments are rejected with their own code on a box without any GPU."""
     fake = ctypes.c_void_p(0x1000)

@@ -109,10 +109,22 @@ def test_quantized_lm_head_vocab_shape(dn, M):
     w_cpu = head.weight.data.cpu()
     head.quantize_(dt, keep_weight=True)
     assert head.weight is not None and head.qw.shape == (V, H)
+    from nanovllm.utils.context import reset_context, set_context
     x = torch.randn(M + 3, H, generator=torch.Generator().manual_seed(M)).to(torch.bfloat16)
-    last = torch.arange(3, M + 3)
-    logits = head(x.cuda(), last.cuda())
+    # the reference's calling convention (embed_head.py:56-66): forward(x), last-token selection
+    # from the prefill context.  M sequences; the first is 4 tokens long, the others 1 token each,
+    # so cu_seqlens_q[1:] - 1 = 3, 4, ..., M + 2.
+    cu = torch.cat([torch.tensor([0]), torch.arange(4, M + 4)]).to(torch.int32).cuda()
+    set_context(True, cu_seqlens_q=cu)
+    try:
+        logits = head(x.cuda())
+    finally:
+        reset_context()
     assert logits.shape == (M, V) and logits.dtype == torch.bfloat16
+    n_dec = min(M, 2)
+    dec = head(x[3:3 + n_dec].cuda())                         # decode: no selection (context.is_prefill False)
+    assert dec.shape == (n_dec, V)
+    assert float((dec.float() - logits[:n_dec].float()).abs().max()) <= 0.02 * float(logits.float().abs().max())
     idx = np.r_[0:300, V // 2:V // 2 + 300, V - 300:V]
     qwo, swo = orc.quant_rows(orc.t2n(w_cpu[idx]), fmt)
     assert np.array_equal(orc.t2n(head.qw[idx]), qwo) and np.array_equal(orc.t2n(head.sw[idx]), swo)
