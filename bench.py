@@ -217,6 +217,7 @@ class LinearStack:
                 self.layers.append(mods)
         torch.set_default_dtype(prev)
         self.tp = self.layers[0][0].tp_size
+        self.side = None
 
     @torch.inference_mode()
     def forward(self, x):
@@ -228,6 +229,43 @@ class LinearStack:
         the sequence-parallel hand-off (RowParallelLinear.forward_quant: GEMM-epilogue
         reduce-scatter -> quantise the owner's tokens -> all-gather codes + scales); the last
         linear returns the all-reduced bf16 tensor (RowParallelLinear.forward)."""
+        T = x.shape[0]
+        nmb = self.micro_batches(T)
+        if nmb == 1:
+            return self._pass(x)
+        # Two token micro-batches on two streams, one collective channel each: the NVLink time,
+        # flag latencies and write acknowledgements of one micro-batch's reduce-scatter / all-gather
+        # hide under the tensor-core work of the other (include/qlinear_b200.h, "PER CHANNEL").
+        from nanovllm.layers.linear import tp_channel
+        cur = torch.cuda.current_stream()
+        if self.side is None:
+            self.side = [torch.cuda.Stream() for _ in range(nmb)]
+        cut = (T // nmb + 255) // 256 * 256                 # whole 256-token tiles per micro-batch
+        outs = []
+        for c in range(nmb):
+            st = self.side[c]
+            st.wait_stream(cur)
+            with torch.cuda.stream(st), tp_channel(c):
+                outs.append(self._pass(x[c * cut: min(T, (c + 1) * cut)]))
+        for st in self.side:
+            cur.wait_stream(st)
+        return torch.cat(outs)
+
+    def micro_batches(self, T):
+        """QL_TP_MICRO=2: two micro-batches when the step is tensor-parallel, prefill-sized and the
+        NVLink path with >= 2 channels is up; default 1 (measured on 2 and 4 B200s the split does not
+        pay on Qwen3-0.6B: half-size GEMMs lose more than the overlap wins, profiles/r2e_*)."""
+        if self.tp == 1 or os.environ.get("QL_TP_MICRO", "1") != "2" or self.layers[0][1].group_size:
+            return 1
+        from nanovllm import _comm
+        comm = _comm.get()
+        if comm is None or comm.channels < 2 or T < 2 * 256 * self.tp:
+            return 1
+        half = (T // 2 + 255) // 256 * 256
+        hid = self.m["hidden"]
+        return 2 if (comm.fits_big(half, hid) and not comm.fits(half * hid)) else 1
+
+    def _pass(self, x):
         m = self.m
         k_o, k_down = m["heads"] * m["hd"] // self.tp, m["inter"] // self.tp
         h_in, last = x, len(self.layers) - 1
@@ -398,6 +436,57 @@ def cpu_reference(m, T, dtype, quant, group, warmup, reps):
 
 # ------------------------------------------------------------------ main
 
+def kernel_table(step, path, rank, dist_on, line, reps=3):
+    """Per-kernel breakdown of one step (all ranks run it; rank 0 writes): kernel name, launches
+    per step, mean and total microseconds, share of the summed kernel time.  Collected with the
+    CUPTI activity tracer (torch.profiler) AFTER the timed runs; its times carry tracer overhead
+    and are for attribution only."""
+    import collections
+    import torch.distributed as dist
+    from torch.profiler import ProfilerActivity, profile
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for _ in range(reps):
+            step()
+        torch.cuda.synchronize()
+    if dist_on:
+        dist.barrier()
+    if rank != 0:
+        return
+    # Kernels overlap under programmatic dependent launch (a kernel's recorded duration includes
+    # its wait on the predecessor), so durations do not add up.  "exposed" partitions the step
+    # instead: end_i - max(start_i, latest end so far), in start order.
+    evs = [ev for ev in prof.events()
+           if ev.device_type is not None and "cuda" in str(ev.device_type).lower()]
+    evs.sort(key=lambda ev: ev.time_range.start)
+    agg = collections.OrderedDict()
+    t0 = evs[0].time_range.start if evs else 0.0
+    t1 = max(ev.time_range.end for ev in evs) if evs else 0.0
+    front, idle = t0, 0.0
+    for ev in evs:
+        tr = ev.time_range
+        d = agg.setdefault(ev.name, [0, 0.0, 0.0])
+        d[0] += 1
+        d[1] += tr.end - tr.start
+        if tr.start > front:
+            idle += tr.start - front
+        d[2] += max(0.0, tr.end - max(tr.start, front))
+        front = max(front, tr.end)
+    span = (t1 - t0) or 1.0
+    with open(path, "w") as f:
+        f.write(f"# {line['config']['workload']}  {line['config']['parallelism']}  ({line['config']['launch']})\n")
+        f.write(f"# timed (no tracer): {line['ms_per_step']:.4f} ms/step, {line['value']:.0f} tokens/s;  under the tracer: "
+                f"{span / reps / 1e3:.4f} ms/step span, {idle / reps / 1e3:.4f} ms/step idle between kernels "
+                f"(rank 0, {reps} steps)\n")
+        f.write("# duration = start..end incl. the wait on the predecessor under PDL (overlaps, does not add up);\n")
+        f.write("# exposed = end - max(start, latest earlier end): partitions the step span\n")
+        f.write("# launches/step | mean duration us | exposed us/launch | exposed us/step | share of span | kernel\n")
+        for name, (n, us, ex) in sorted(agg.items(), key=lambda kv: -kv[1][2]):
+            f.write(f"{n / reps:8.1f} | {us / n:9.2f} | {ex / n:9.2f} | {ex / reps:10.1f} | {ex / span:6.3f} | {name[:150]}\n")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -411,6 +500,9 @@ def main():
     ap.add_argument("--group-size", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--kernel-table", default=None, metavar="PATH",
+                    help="AFTER the line is printed: replay 3 steps under the CUPTI kernel tracer and write "
+                         "per-kernel-name mean durations (rank 0) -- a breakdown for profiles/, never a bench value")
     args = ap.parse_args()
 
     m = MODELS[args.model]
@@ -650,6 +742,10 @@ def main():
     if tp_info is not None:
         line["tp_check"] = tp_info["status"]
         line["tp_collective"] = tp_info
+        nmb = stack.micro_batches(T)
+        config["tp_micro_batches"] = nmb
+        config["tp_pipeline"] = ("2 token micro-batches on 2 streams, one NVLink collective channel each"
+                                 if nmb > 1 else "single stream")
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         T_s = min(T_rank, 4096)
         tok_s, ts, cores = cpu_reference(m, T_s, dtype, args.quant, group, 1, 2)
@@ -659,6 +755,11 @@ def main():
                                           "(reference per_group_matmul semantics)"}
     if rank == 0:
         print(json.dumps(line), flush=True)
+    if args.kernel_table:
+        try:
+            kernel_table(step_dev, args.kernel_table, rank, dist_on, line)
+        except Exception as e:  # noqa: BLE001 -- attribution only; the line above is already out
+            print(f"kernel table failed: {e!r}", file=sys.stderr, flush=True)
     if dist_on:
         # The captured graphs hold NCCL kernels; tearing the communicator down under them hung
         # the first TP=2 run after the line was printed (profiles/r1o_*).  Everything is measured

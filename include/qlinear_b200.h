@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define QL_ABI_VERSION 6
+#define QL_ABI_VERSION 8
 
 /* status codes */
 #define QL_OK 0
@@ -238,7 +238,7 @@ QL_API int ql_ar_rmsnorm_quant(const void* partial, const void* residual_in, voi
  * in fp32 in rank order, rounds once to bf16, quantises its tokens and sends codes + scales to
  * every rank, whose next column-parallel GEMM reads them through ql_gemm_w8a8.
  *   ql_tp_max_tokens / ql_tp_max_hidden: capacity given to ql_ar_init (0 = path unavailable);
- *   ql_tp_buffer(which): this rank's buffers inside the symmetric area (device pointers that stay
+ *   ql_tp_buffer(which, channel): this rank's buffers inside the symmetric area (device pointers that stay
  *     valid until ql_ar_destroy): 0 = bf16 partial [M, N] dense (write the row-parallel GEMM's
  *     output here for pushed = 0), 1 = gathered codes [M, N], 2 = gathered scales fp32 [M];
  *   ql_tp_gemm_push: the row-parallel W8A8 GEMM (per-row scales, as ql_gemm_w8a8) whose epilogue
@@ -251,7 +251,13 @@ QL_API int ql_ar_rmsnorm_quant(const void* partial, const void* residual_in, voi
  *   ql_tp_allreduce_bf16(M, N, pushed, out, ldo): same reduction, bf16 rows gathered instead; the
  *     complete [M, N] result is written to the local tensor `out` (dist.all_reduce semantics).
  * M <= ql_tp_max_tokens(), N <= ql_tp_max_hidden(), N % 8 == 0.  Same calling rules as
- * ql_ar_allreduce_bf16 (every rank, same order, same shapes; CUDA-graph safe).
+ * ql_ar_allreduce_bf16 (every rank, same order, same shapes; CUDA-graph safe) -- PER CHANNEL:
+ * `channel` (0 .. ql_tp_channels()-1) selects one of the independent sets of buffers, flags and
+ * call counters.  A caller that splits a prefill batch into two token micro-batches and runs them
+ * on two streams, one channel each, hides the wire time, flag latency and write acknowledgements
+ * of one micro-batch's collective under the other's GEMMs: the reduce kernel is one 128-thread CTA
+ * per SM and stays co-resident with a CTA-pair GEMM (per-row / per-tensor scales; do not use two
+ * channels concurrently with per-group linears, whose GEMM does not leave room for it).
  */
 /*
  * Test hook: a W-rank communicator emulated on ONE GPU (the driver's GPU test tier has a single
@@ -266,15 +272,62 @@ QL_API int ql_tp_emu_set_rank(int rank);
 
 QL_API size_t ql_tp_max_tokens(void);
 QL_API size_t ql_tp_max_hidden(void);
-QL_API void* ql_tp_buffer(int which);
+/*
+ *   ql_tp_set_concurrent(on): declare that two channels will be in flight at the same time (also
+ *     implied by the first call on a channel > 0).  The reduce kernels then release their stream's
+ *     next kernel only after their last cross-GPU wait: a GEMM parked behind a reduce kernel that
+ *     waits for a peer would otherwise hold the shared memory the other channel's GEMM -- the one
+ *     the peer is waiting for -- needs.  Call it before capturing CUDA graphs of channel 0.
+ */
+QL_API int ql_tp_channels(void);
+QL_API int ql_tp_set_concurrent(int on);
+QL_API void* ql_tp_buffer(int which, int channel);
 QL_API int ql_tp_gemm_push(const void* qx, const float* sx, const void* qw, const float* sw,
-                    const void* bias, int64_t M, int64_t N, int64_t K, int fmt, ql_stream_t stream);
-QL_API int ql_tp_reduce_quant_gather(int64_t M, int64_t N, int fmt, int pushed, ql_stream_t stream);
-QL_API int ql_tp_allreduce_bf16(int64_t M, int64_t N, int pushed, void* out, int64_t ldo,
+                    const void* bias, int64_t M, int64_t N, int64_t K, int fmt, int channel,
+                    ql_stream_t stream);
+QL_API int ql_tp_reduce_quant_gather(int64_t M, int64_t N, int fmt, int pushed, int channel,
+                              ql_stream_t stream);
+QL_API int ql_tp_allreduce_bf16(int64_t M, int64_t N, int pushed, void* out, int64_t ldo, int channel,
                          ql_stream_t stream);
 
 /* Bytes of caller-provided scratch ql_linear needs for an [M, K] activation (0 for M <= 16). */
 QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);
+
+/*
+ * Decode-regime CHAIN of quantized linears in one persistent launch (csrc/decode_chain.cu).
+ * Replaces, for M <= 16 tokens, the per-linear per_row_quant + per_row_matmul launches of the
+ * reference's decode step (nanovllm/utils/quantization.py:310-346, called from the four linears of
+ * every decoder layer, nanovllm/models/qwen3.py:80,90,116,118) wherever one quantized linear feeds
+ * the next: op i with x == NULL consumes the first K_i columns of op i-1's output y (row pitch
+ * ldy of that op); an op with x != NULL reads its own bf16 input [M, ldx] (the first op must).
+ * Every op is y = bf16((acc * sx[m]) * sw[n] + bias[n]) on per-token-quantised x, per-row weight
+ * scales, exactly as ql_linear (INT8: bit-identical; FP8: fp32 summation order differs).
+ *   ql_chain_workspace_bytes: device scratch the chain needs (0 = the chain is not supported:
+ *     M > 16, K % 128, N % 8, a slice plan that does not fit ...);
+ *   ql_chain_prepare: plans the chain for the current device, writes the device-side descriptors
+ *     into `workspace` (256-byte aligned, stays owned by the caller, must outlive every run) and
+ *     fills `plan`; synchronises `stream`; NOT capturable.  The op array, M, every pointer and
+ *     pitch are frozen into the workspace: prepare again when any of them changes;
+ *   ql_chain_run: ONE kernel launch (cooperative: one CTA per SM, all co-resident); capturable
+ *     into a CUDA graph.  Runs of one workspace must not overlap each other.
+ * group must be 0 (per-group scales: use ql_linear).
+ */
+typedef struct ql_chain_op {
+  const void* qw;     /* [N, K] codes, row-major, 16-byte aligned */
+  const float* sw;    /* [N] weight scales */
+  const void* bias;   /* bf16 [N] or NULL */
+  const void* x;      /* bf16 [M, ldx], or NULL = previous op's y */
+  void* y;            /* bf16 [M, ldy] */
+  int64_t ldx, ldy;   /* row pitches in elements (ldx ignored when x == NULL) */
+  int64_t N, K;
+} ql_chain_op;
+typedef struct ql_chain_plan {
+  unsigned char opaque[128];
+} ql_chain_plan;
+QL_API size_t ql_chain_workspace_bytes(const ql_chain_op* ops, int n_ops, int64_t M);
+QL_API int ql_chain_prepare(const ql_chain_op* ops, int n_ops, int64_t M, int fmt, int64_t group,
+                            void* workspace, size_t workspace_bytes, ql_chain_plan* plan, ql_stream_t stream);
+QL_API int ql_chain_run(const ql_chain_plan* plan, void* workspace, ql_stream_t stream);
 
 /* Name of the kernel family ql_linear would pick ("gemv_mma", "gemm_tcgen05"); for logs/tests. */
 QL_API const char* ql_linear_path(int64_t M, int64_t N, int64_t K, int64_t group);

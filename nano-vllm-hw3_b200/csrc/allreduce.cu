@@ -44,7 +44,7 @@ struct ArState {
 static ArState g_ar;
 
 // area layout: [parity 0: W regions of 2*bytes][parity 1: same][epoch u32][done u32] (256 B)
-//              [big section, 4 KB aligned: flags 4 KB | partial | codes | scales | bf16 gather]
+//              [big section x kTpChannels, 4 KB aligned: flags 4 KB | partial | codes | scales | bf16 gather]
 static size_t ar_region_bytes(size_t bytes) { return 2 * bytes; }          // 8 B packet per 4 B payload
 static size_t ar_ctr_offset(size_t bytes, int world) { return 2 * (size_t)world * ar_region_bytes(bytes); }
 static size_t ar_big_offset(size_t bytes, int world) { return (ar_ctr_offset(bytes, world) + 256 + 4095) & ~(size_t)4095; }
@@ -65,9 +65,21 @@ static size_t ar_alloc_bytes(size_t bytes, int world, size_t rows, size_t hidden
   if (rows > 0 && hidden > 0) {
     TpLayout L;
     big_layout(rows, hidden, world, &L);
-    total += L.total;
+    total += kTpChannels * rup(L.total, 4096);
   }
   return total;
+}
+
+// flags and call counters of every channel start at epoch 0
+static bool big_clear_flags(uint8_t* area, size_t bytes, int world, size_t rows, size_t hidden) {
+  if (rows == 0 || hidden == 0) return true;
+  TpLayout L;
+  big_layout(rows, hidden, world, &L);
+  for (int c = 0; c < kTpChannels; ++c)
+    if (cudaMemset(area + ar_big_offset(bytes, world) + (size_t)c * rup(L.total, 4096) + L.flags, 0, 4096) !=
+        cudaSuccess)
+      return false;
+  return true;
 }
 
 struct ArParams {
@@ -179,11 +191,11 @@ bool ar_view(ArView* v) {
   return true;
 }
 
-bool tp_view(TpView* v) {
-  if (!g_ar.ready || g_ar.big_rows == 0) return false;
-  const size_t off = ar_big_offset(g_ar.bytes, g_ar.world);
-  for (int r = 0; r < kArMaxWorld; ++r) v->big[r] = r < g_ar.world ? g_ar.peer[r] + off : nullptr;
+bool tp_view(TpView* v, int channel) {
+  if (!g_ar.ready || g_ar.big_rows == 0 || channel < 0 || channel >= kTpChannels) return false;
   big_layout(g_ar.big_rows, g_ar.big_hidden, g_ar.world, &v->lay);
+  const size_t off = ar_big_offset(g_ar.bytes, g_ar.world) + (size_t)channel * rup(v->lay.total, 4096);
+  for (int r = 0; r < kArMaxWorld; ++r) v->big[r] = r < g_ar.world ? g_ar.peer[r] + off : nullptr;
   v->rows = g_ar.big_rows;
   v->rows_cap = big_rows_cap(g_ar.big_rows, g_ar.world);
   v->hidden = g_ar.big_hidden;
@@ -232,8 +244,9 @@ int ql_ar_init(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int world, 
   uint8_t* ptr = nullptr;
   if (cudaMalloc(&ptr, total) != cudaSuccess) { (void)cudaGetLastError(); return QL_ERR_CUDA; }
   // only the packet regions, counters and flags need a defined initial state (epoch 0)
-  const size_t head = ar_big_offset(max_bytes, world) + (rs_tokens ? 4096 : 0);
-  if (cudaMemset(ptr, 0, head) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
+  const size_t head = ar_big_offset(max_bytes, world);
+  if (cudaMemset(ptr, 0, head) != cudaSuccess || !big_clear_flags(ptr, max_bytes, world, rs_tokens, rs_hidden) ||
+      cudaDeviceSynchronize() != cudaSuccess) {
     (void)cudaGetLastError();
     cudaFree(ptr);
     return QL_ERR_CUDA;
@@ -284,10 +297,11 @@ int ql_ar_init_local(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int w
   if (g_ar.local != nullptr) return QL_ERR_BAD_SHAPE;
   if (int e = ql_device_check()) return e;
   const size_t total = ar_alloc_bytes(max_bytes, world, rs_tokens, rs_hidden);
-  const size_t head = ar_big_offset(max_bytes, world) + 4096;
+  const size_t head = ar_big_offset(max_bytes, world);
   for (int r = 0; r < world; ++r) {
     uint8_t* ptr = nullptr;
-    if (cudaMalloc(&ptr, total) != cudaSuccess || cudaMemset(ptr, 0, head) != cudaSuccess) {
+    if (cudaMalloc(&ptr, total) != cudaSuccess || cudaMemset(ptr, 0, head) != cudaSuccess ||
+        !big_clear_flags(ptr, max_bytes, world, rs_tokens, rs_hidden)) {
       (void)cudaGetLastError();
       if (ptr != nullptr) cudaFree(ptr);
       for (int k = 0; k < r; ++k) { cudaFree(g_ar.peer[k]); g_ar.peer[k] = nullptr; }

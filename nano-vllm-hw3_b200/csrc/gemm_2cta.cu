@@ -48,10 +48,10 @@ struct Gemm2Params {
 // Fused reduce-scatter (PUSH): where the tiles go and whom to tell.
 struct Gemm2Push {
   CUtensorMap ymap[8];        // per token owner: its receive region for THIS rank's partials, [rows_o, N] bf16
-  uint32_t* ready_slot[8];    // ready[this rank] in every rank's flag block (peer-mapped)
-  uint32_t* ctr;              // local {epoch, rows_done, gemm_done, copy_done}
   int tiles_per_owner;        // 256-token tiles per owner slice
-  int world;
+  int rot;                    // token-tile rotation: rank r starts with owner r+1's tiles and ends with its own,
+                              // so at any moment the W senders address W different receivers and the local
+                              // (wire-free) tiles are the tail
 };
 
 constexpr int kG2Threads = 384;   // 4 control warps + 8 epilogue warps
@@ -233,6 +233,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
         for (int tile = pair; tile < total_tiles && pre < kG2Stages; tile += num_pairs) {
           int tm, tn;
           tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+          if constexpr (PUSH) { tm += push->rot; if (tm >= p.tiles_m) tm -= p.tiles_m; }
           const int row_b = tn * kG2TileN + (int)cta * kG2RowsB;
           for (int kb = 0; kb < num_kb && pre < kG2Stages; ++kb, ++pre, ++stage) {
             const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[stage]), 0);
@@ -248,6 +249,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
       for (int tile = pair; tile < total_tiles; tile += num_pairs) {
         int tm, tn;
         tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+          if constexpr (PUSH) { tm += push->rot; if (tm >= p.tiles_m) tm -= p.tiles_m; }
         const int row_a = tm * 2 * kG2RowsA + (int)cta * kG2RowsA;
         const int row_b = tn * kG2TileN + (int)cta * kG2RowsB;
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
@@ -319,6 +321,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       int tm, tn;
       tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+          if constexpr (PUSH) { tm += push->rot; if (tm >= p.tiles_m) tm -= p.tiles_m; }
       const int n0 = tn * kG2TileN + half * 128;                          // first feature of this warp
       const int m0 = tm * 2 * kG2RowsA + (int)cta * kG2RowsA + q * 32;   // first token of this warp
       const int m = m0 + lane;
@@ -420,34 +423,25 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
       if (lane == 0) mbar_arrive_cluster(tempty_leader0 + acc * 8);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    // PUSH: the CTA only waits until the store engine has READ its staging tiles, not for the
+    // peers' write acknowledgements (a NVLink round trip): the grid does not complete before its
+    // bulk stores have, and the reduce kernel behind it in the stream signals the peers -- the SM
+    // is free for the other channel's GEMM meanwhile.
     if (lane == 0) {
-      tma_store_wait_all();
-      if constexpr (PUSH) asm volatile("fence.proxy.async.global;" ::: "memory");
+      if constexpr (PUSH) tma_store_wait_read<0>(); else tma_store_wait_all();
     }
   }
 
   tc_fence_before();
   cluster_sync_all();
   if (warp == 2) tmem_dealloc2(tmem_base, 512);
-  if constexpr (PUSH) {
-    // Every tile of this CTA has landed in its owner's memory (bulk stores waited for above).
-    // The last CTA of the grid raises ready[this rank] = call number on every rank; the owners'
-    // reduce kernels (tp_collective.cu) poll it.  Thread 0 is the TMA producer: it has passed
-    // griddepcontrol.wait, so the call counter it reads is final.
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      if (atomicAdd(push->ctr + 2, 1u) == gridDim.x - 1) {
-        push->ctr[2] = 0;
-        const uint32_t e = *reinterpret_cast<volatile uint32_t*>(push->ctr) + 1;
-        __threadfence_system();
-        for (int r = 0; r < push->world; ++r) st_release_sys(push->ready_slot[r], e);
-      }
-    }
-  }
 }
 
+// 128 registers x 384 threads leave a quarter of the register file free: the tensor-parallel
+// reduce kernel of the OTHER channel (tp_collective.cu, 128 threads) stays co-resident with a GEMM
+// CTA, which the two-channel pipeline relies on (no spills at this bound).
 template <int FMT, bool OUT_ACC, bool HAS_BIAS>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kG2Threads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
 gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
              const __grid_constant__ CUtensorMap tm_y, const Gemm2Params p) {
   gemm2_body<FMT, OUT_ACC, HAS_BIAS, false>(tm_x, tm_w, &tm_y, p, nullptr);
@@ -456,7 +450,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ C
 // GEMM + reduce-scatter over NVLink in one kernel: UTC*MMA tiles whose epilogue TMA-stores into
 // peer memory (see Gemm2Push).
 template <int FMT, bool HAS_BIAS>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kG2Threads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
 gemm2_push_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                   const __grid_constant__ Gemm2Push push, const Gemm2Params p) {
   gemm2_body<FMT, false, HAS_BIAS, true>(tm_x, tm_w, nullptr, p, &push);
@@ -554,7 +548,6 @@ static int launch_g2_push(const TpView& tp, const void* qx, const void* qw, Gemm
   Gemm2Push push;
   const int64_t Mo = tp_rows_per_owner(p.M, tp.world);
   for (int o = 0; o < 8; ++o) {
-    push.ready_slot[o] = nullptr;
     if (o >= tp.world) { push.ymap[o] = tm_x; continue; }
     int64_t rows_o = (int64_t)p.M - o * Mo;
     rows_o = rows_o < 1 ? 1 : (rows_o > Mo ? Mo : rows_o);       // an owner without rows is never addressed
@@ -562,17 +555,17 @@ static int launch_g2_push(const TpView& tp, const void* qx, const void* qw, Gemm
     if (!make_tmap_2d(&push.ymap[o], base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, p.N, rows_o, (int64_t)p.N * 2,
                       kG2StoreCols, 32))
       return QL_ERR_CUDA;
-    push.ready_slot[o] = reinterpret_cast<uint32_t*>(tp.big[o] + tp.lay.flags + kTpReadyOff +
-                                                     (size_t)tp.rank * kTpFlagStride);
   }
-  push.ctr = reinterpret_cast<uint32_t*>(tp.big[tp.rank] + tp.lay.flags + kTpCtrOff);
   push.tiles_per_owner = (int)(Mo / (2 * kG2RowsA));
-  push.world = tp.world;
+  push.rot = 0;   // set below, once tiles_m is known
   p.tiles_m = (p.M + 2 * kG2RowsA - 1) / (2 * kG2RowsA);
   p.tiles_n = (p.N + kG2TileN - 1) / kG2TileN;
+  // one owner's token tiles form a rasterisation group: the grid works through the owners one
+  // after the other (all feature tiles of owner r+1, then r+2, ..., its own last)
+  p.group_m = push.tiles_per_owner < p.tiles_m ? push.tiles_per_owner : p.tiles_m;
   {
-    const int64_t g = (48ll << 20) / (256ll * p.K);
-    p.group_m = (int)(g < 1 ? 1 : (g > p.tiles_m ? p.tiles_m : g));
+    const int64_t first = (int64_t)((tp.rank + 1) % tp.world) * push.tiles_per_owner;
+    push.rot = first < p.tiles_m ? (int)first : 0;       // an owner without tokens: start at owner 0
   }
   const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
   const int pairs_max = g2_pairs_max(reinterpret_cast<const void*>(kern));

@@ -392,17 +392,56 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
+// A tensor map is a pure function of its arguments (the driver call touches no device state), so
+// the descriptors of the eager path -- the same weights, activations and outputs every step -- are
+// kept in a small per-thread direct-mapped cache instead of being re-encoded on every launch.
+struct TmapKey {
+  const void* base;
+  int64_t inner, outer, stride;
+  int dt, box_inner, box_outer;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && inner == o.inner && outer == o.outer && stride == o.stride && dt == o.dt &&
+           box_inner == o.box_inner && box_outer == o.box_outer;
+  }
+};
+struct TmapSlot {
+  TmapKey key;
+  bool valid;
+  CUtensorMap map;
+};
+constexpr int kTmapSlots = 1024;   // power of two; 28 layers x 4 linears x 3 maps fit several times over
+
+static inline uint32_t tmap_hash(const TmapKey& k) {
+  uint64_t h = reinterpret_cast<uint64_t>(k.base) * 0x9E3779B97F4A7C15ull;
+  h ^= (uint64_t)k.outer * 0xC2B2AE3D27D4EB4Full + (uint64_t)k.inner * 0x165667B19E3779F9ull;
+  h ^= ((uint64_t)k.stride << 20) ^ ((uint64_t)k.box_outer << 8) ^ (uint64_t)k.box_inner ^ ((uint64_t)k.dt << 40);
+  return (uint32_t)(h >> 40) & (kTmapSlots - 1);
+}
+
 bool make_tmap_2d(CUtensorMap* tm, const void* base, CUtensorMapDataType dt, int64_t inner,
                   int64_t outer, int64_t row_stride_bytes, int box_inner, int box_outer) {
+  static thread_local TmapSlot* cache = nullptr;
+  if (cache == nullptr) cache = new TmapSlot[kTmapSlots]();   // lives as long as the thread's launches
+  const TmapKey key{base, inner, outer, row_stride_bytes, (int)dt, box_inner, box_outer};
+  TmapSlot& slot = cache[tmap_hash(key)];
+  if (slot.valid && slot.key == key) {
+    *tm = slot.map;
+    return true;
+  }
   EncodeTiledFn fn = encode_fn();
   if (fn == nullptr) return false;
   cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
   cuuint64_t gstride[1] = {(cuuint64_t)row_stride_bytes};
   cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
   cuuint32_t estr[2] = {1, 1};
-  return fn(tm, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  if (fn(tm, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  slot.key = key;
+  slot.map = *tm;
+  slot.valid = true;
+  return true;
 }
 
 // 2-D uint8 tensor [rows, K] (K contiguous), box = {128 K-bytes, box_rows}

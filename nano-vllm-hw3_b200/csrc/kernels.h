@@ -64,7 +64,7 @@ int launch_ar_rmsnorm_quant(const ArView& ar, const void* partial, const void* r
 // The "big" section of the symmetric area: the reduce-scatter / all-gather path behind prefill-
 // sized row-parallel linears (tp_collective.cu).  Offsets are relative to a rank's big section.
 struct TpLayout {
-  size_t flags;   // 4 KB: ready[8] (128 B apart) | +1024: done[8] | +2048: {epoch, rows_done, gemm_done, copy_done}
+  size_t flags;   // 4 KB: ready[8] (128 B apart) | +1024: done[8] | +2048: {epoch, rows_done, -, copy_done}
   size_t part;    // bf16 partial sums: [rows_cap, N] of this rank (pull) or W receive regions (push)
   size_t q;       // gathered codes  [rows_cap, N] 1 B
   size_t s;       // gathered scales [rows_cap] fp32
@@ -79,7 +79,12 @@ struct TpView {
   int world, rank;
   bool emulated;        // all ranks live in this process: one launch runs them all (tests)
 };
-bool tp_view(TpView* v);   // false unless ql_ar_init was given a large-path capacity and ql_ar_open succeeded
+// false unless ql_ar_init was given a large-path capacity and ql_ar_open succeeded.  `channel`
+// selects one of kTpChannels independent sets of buffers, flags and call counters: two token
+// micro-batches on two streams keep one collective in flight each, so the wire time of one hides
+// under the GEMMs of the other.
+constexpr int kTpChannels = 2;
+bool tp_view(TpView* v, int channel = 0);
 constexpr size_t kTpReadyOff = 0, kTpDoneOff = 1024, kTpCtrOff = 2048, kTpFlagStride = 128;
 // rows per token owner: whole 256-token pair tiles, so that a GEMM tile never straddles two owners
 inline int64_t tp_rows_per_owner(int64_t M, int world) {
@@ -94,7 +99,8 @@ int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* s
 bool gemm2_eligible(const void* y, int64_t ldy, const void* sw, const void* bias, bool out_acc);
 // The same kernel as a fused GEMM + reduce-scatter over NVLink: every 256-token output tile is
 // TMA-stored into the receive region of the rank that owns those tokens (peer memory), and the last
-// CTA to finish raises this rank's `ready` flag on every peer.  M rows in total, owner slices of
+// reduce kernel that follows in the stream raises this rank's `ready` flag on every peer once the
+// grid (and with it every bulk store) has completed.  M rows in total, owner slices of
 // tp_rows_per_owner(M, world) rows.
 int launch_gemm2_push(const TpView& tp, const void* qx, const float* sx, const void* qw, const float* sw,
                       const void* bias, int64_t M, int64_t N, int64_t K, int fmt, cudaStream_t st);

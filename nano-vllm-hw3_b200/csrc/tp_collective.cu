@@ -6,7 +6,7 @@
 // called from per_row_matmul :323).  NCCL's ring all-reduce moves 2 * 2 B * (W-1)/W per element
 // and every rank then quantises all W*T tokens again; here
 //   1. every rank's bf16 partial sums reach the rank that OWNS a token (reduce-scatter): either
-//      pushed tile by tile from the GEMM epilogue (gemm2_kernel<PUSH>, TMA stores into the owner's
+//      pushed tile by tile from the GEMM epilogue (gemm2_push_kernel, TMA stores into the owner's
 //      receive region while the tensor core works on the next tile) or pulled by the owner;
 //   2. the owner adds the W partials in fp32 in rank order, rounds once to bf16 -- identical on
 //      every rank, deterministic, more accurate than NCCL's bf16 ring -- and quantises ITS tokens
@@ -20,9 +20,13 @@
 // the peers and polled locally with ld.acquire.sys: ready[src] = "src's partials for call e are
 // in place", done[src] = "src has delivered everything it owns for call e".  The call number e
 // is a device-side counter advanced by the last block, so the kernels replay inside CUDA graphs.
-// Buffers are single: a rank can start call e+1's pushes only after its own call-e kernel saw
-// every done flag, i.e. after every peer finished reading call e's partials.
-// Every rank must issue the same sequence of calls with the same shapes.
+// Buffers are single per CHANNEL: a rank can start call e+1's pushes only after its own call-e
+// kernel saw every done flag, i.e. after every peer finished reading call e's partials.  Every
+// rank must issue the same sequence of calls with the same shapes on a channel.  The kTpChannels
+// channels are independent (own buffers, flags, counters): two token micro-batches on two streams
+// keep one collective each in flight, and because this kernel is launched with at most one small
+// CTA per SM it stays co-resident with the other channel's GEMM -- flag latencies, write
+// acknowledgements and wire time of one micro-batch hide under the tensor-core work of the other.
 #include <cuda.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -44,6 +48,7 @@ struct TpArgs {
   int64_t ldo;
   int64_t out_rank_stride;   // emulation: elements between the ranks' `out` tensors
   uint64_t timeout_ns;
+  int late_pdl;          // channels run concurrently: release the stream's next kernel only after the cross-GPU waits
 };
 
 template <int FMT> struct TpQ { static constexpr float qmax = 1.0f; };
@@ -82,10 +87,16 @@ __device__ __forceinline__ void tp_wait_flags(uint8_t* my_big, size_t base, int 
 }
 
 template <int FMT, int W, int NV, int WPR>
-__global__ void __launch_bounds__(TpRowCfg<WPR>::threads)
+// <= 128 registers x 128 threads: fits next to a 384-thread, 128-register GEMM CTA on one SM
+__global__ void __launch_bounds__(TpRowCfg<WPR>::threads, 4)
 tp_reduce_kernel(const TpArgs a) {
   __shared__ float red[8];
-  pdl_launch_dependents();
+  // With one channel the next kernel of the stream may start (and park at its griddepcontrol.wait)
+  // right away.  With two channels on two streams it must not: a parked GEMM holds its SM's shared
+  // memory while this kernel waits for a PEER's GEMM -- if the peer is in the mirrored state on the
+  // other channel, neither rank can place the GEMM the other one waits for.  Then the dependents
+  // are released after the last cross-GPU wait instead.
+  if (!a.late_pdl) pdl_launch_dependents();
   pdl_wait();                       // this rank's GEMM (its partial sums / its pushes) is complete
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int ROWS = TpRowCfg<WPR>::rows;
@@ -97,8 +108,10 @@ tp_reduce_kernel(const TpArgs a) {
   const int nvec = a.N >> 3;
 
   // ---- 1. the partials of call e are in place on every rank ---------------------------------
-  if (!a.pushed && blockIdx.x == 0 && threadIdx.x < W && (int)threadIdx.x != rank) {
-    __threadfence_system();         // (the GEMM's stores are complete: previous kernel)
+  // (the GEMM grid in front of this kernel has completed, and with it its stores -- the bulk
+  //  stores into the owners' receive regions in the pushed form)
+  if (blockIdx.x == 0 && threadIdx.x < W && (int)threadIdx.x != rank) {
+    __threadfence_system();
     st_release_sys(tp_flag(a.big[threadIdx.x], a.lay.flags + kTpReadyOff, rank), e);
   }
   tp_wait_flags<W>(mine, a.lay.flags + kTpReadyOff, rank, e, a.timeout_ns);
@@ -200,6 +213,7 @@ tp_reduce_kernel(const TpArgs a) {
     }
   }
   tp_wait_flags<W>(mine, a.lay.flags + kTpDoneOff, rank, e, a.timeout_ns);
+  if (a.late_pdl) pdl_launch_dependents();
 
   if constexpr (FMT == QL_FMT_BF16) {
     // the peers' rows sit in my gather buffer: copy them next to my own rows in `out`
@@ -243,20 +257,23 @@ template <int FMT, int W, int NV, int WPR>
 static int launch_tp_cfg(const TpArgs& a, cudaStream_t st) {
   auto kern = tp_reduce_kernel<FMT, W, NV, WPR>;
   constexpr int threads = TpRowCfg<WPR>::threads;
-  // all blocks wait on cross-GPU flags, so the grid must be co-resident
-  static int per_sm[64];
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return QL_ERR_CUDA;
-  if (per_sm[dev] == 0) {
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, threads, 0) != cudaSuccess || n < 1) {
+  // All blocks wait on cross-GPU flags, so the grid must be co-resident; and it must stay small
+  // enough to share the SMs with a GEMM of the other channel (one 384-thread CTA per SM holding
+  // ~200 KB of shared memory and most of the register file): QL_TP_REDUCE_CTAS CTAs per SM,
+  // default 1.
+  static int per_sm = 0;
+  if (per_sm == 0) {
+    const char* e = getenv("QL_TP_REDUCE_CTAS");
+    int n = e ? atoi(e) : 1;
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, 0) != cudaSuccess || occ < 1) {
       (void)cudaGetLastError();
-      n = 1;
+      occ = 1;
     }
-    per_sm[dev] = n;
+    per_sm = n < 1 ? 1 : (n > occ ? occ : n);
   }
   const int64_t want = (a.Mo + TpRowCfg<WPR>::rows - 1) / TpRowCfg<WPR>::rows;
-  int64_t blocks = (int64_t)num_sms() * per_sm[dev] / (a.rank < 0 ? W : 1);   // emulation: W ranks share the GPU
+  int64_t blocks = (int64_t)num_sms() * per_sm / (a.rank < 0 ? W : 1);   // emulation: W ranks share the GPU
   if (blocks > want) blocks = want;
   if (blocks < 1) blocks = 1;
   cudaLaunchConfig_t cfg = {};
@@ -297,9 +314,13 @@ static int launch_tp_fmt(const TpArgs& a, int world, cudaStream_t st) {
   }
 }
 
+// set once two channels are in use (ql_tp_set_concurrent, or any call on a channel > 0)
+static int g_tp_concurrent = 0;
+
 int launch_tp_reduce(const TpView& tp, int64_t M, int64_t N, int fmt, int pushed, void* out, int64_t ldo,
                      cudaStream_t st) {
   TpArgs a;
+  a.late_pdl = __atomic_load_n(&g_tp_concurrent, __ATOMIC_RELAXED);
   for (int r = 0; r < 8; ++r) a.big[r] = tp.big[r];
   a.lay = tp.lay;
   a.M = M;
@@ -340,9 +361,16 @@ size_t ql_tp_max_hidden(void) {
   return tp_view(&tp) ? tp.hidden : 0;
 }
 
-void* ql_tp_buffer(int which) {
+int ql_tp_channels(void) { return kTpChannels; }
+
+int ql_tp_set_concurrent(int on) {
+  __atomic_store_n(&g_tp_concurrent, on ? 1 : 0, __ATOMIC_RELAXED);
+  return QL_OK;
+}
+
+void* ql_tp_buffer(int which, int channel) {
   TpView tp;
-  if (!tp_view(&tp)) return nullptr;
+  if (!tp_view(&tp, channel)) return nullptr;
   uint8_t* b = tp.big[tp.rank];
   switch (which) {
     case 0: return b + tp.lay.part;
@@ -352,18 +380,23 @@ void* ql_tp_buffer(int which) {
   }
 }
 
-int ql_tp_reduce_quant_gather(int64_t M, int64_t N, int fmt, int pushed, ql_stream_t stream) {
+int ql_tp_reduce_quant_gather(int64_t M, int64_t N, int fmt, int pushed, int channel, ql_stream_t stream) {
   if (fmt != QL_INT8 && fmt != QL_FP8_E4M3) return QL_ERR_BAD_FORMAT;
+  if (channel < 0 || channel >= kTpChannels) return QL_ERR_BAD_SHAPE;
+  if (channel > 0) __atomic_store_n(&g_tp_concurrent, 1, __ATOMIC_RELAXED);
   TpView tp;
-  if (!tp_view(&tp)) return QL_ERR_WORKSPACE;
+  if (!tp_view(&tp, channel)) return QL_ERR_WORKSPACE;
   if (int e = tp_check_shape(tp, M, N)) return e;
   if (M == 0) return QL_OK;
   return launch_tp_reduce(tp, M, N, fmt, pushed ? 1 : 0, nullptr, 0, (cudaStream_t)stream);
 }
 
-int ql_tp_allreduce_bf16(int64_t M, int64_t N, int pushed, void* out, int64_t ldo, ql_stream_t stream) {
+int ql_tp_allreduce_bf16(int64_t M, int64_t N, int pushed, void* out, int64_t ldo, int channel,
+                         ql_stream_t stream) {
+  if (channel < 0 || channel >= kTpChannels) return QL_ERR_BAD_SHAPE;
+  if (channel > 0) __atomic_store_n(&g_tp_concurrent, 1, __ATOMIC_RELAXED);
   TpView tp;
-  if (!tp_view(&tp)) return QL_ERR_WORKSPACE;
+  if (!tp_view(&tp, channel)) return QL_ERR_WORKSPACE;
   if (int e = tp_check_shape(tp, M, N)) return e;
   if (ldo < N) return QL_ERR_BAD_SHAPE;
   if (M == 0) return QL_OK;
@@ -373,11 +406,13 @@ int ql_tp_allreduce_bf16(int64_t M, int64_t N, int pushed, void* out, int64_t ld
 }
 
 int ql_tp_gemm_push(const void* qx, const float* sx, const void* qw, const float* sw, const void* bias,
-                    int64_t M, int64_t N, int64_t K, int fmt, ql_stream_t stream) {
+                    int64_t M, int64_t N, int64_t K, int fmt, int channel, ql_stream_t stream) {
   if (fmt != QL_INT8 && fmt != QL_FP8_E4M3) return QL_ERR_BAD_FORMAT;
   if (M < 0 || N <= 0 || K <= 0 || K % 128 != 0) return QL_ERR_BAD_SHAPE;
+  if (channel < 0 || channel >= kTpChannels) return QL_ERR_BAD_SHAPE;
+  if (channel > 0) __atomic_store_n(&g_tp_concurrent, 1, __ATOMIC_RELAXED);
   TpView tp;
-  if (!tp_view(&tp)) return QL_ERR_WORKSPACE;
+  if (!tp_view(&tp, channel)) return QL_ERR_WORKSPACE;
   if (int e = tp_check_shape(tp, M, N)) return e;
   if (M == 0) return QL_OK;
   if (!qx || !sx || !qw || !sw) return QL_ERR_NULL;

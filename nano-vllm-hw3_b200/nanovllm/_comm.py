@@ -19,6 +19,11 @@ refused, out of memory, different sizes per rank) every rank frees what it mappe
 
 ``QL_PEER_AR=0`` disables everything here; ``QL_TP_BIG=0`` only the prefill-sized path;
 ``QL_TP_PUSH=0`` makes the owners pull the partials instead of the GEMM pushing them.
+
+The prefill-sized path has ``ql_tp_channels()`` independent channels (own buffers, flags, call
+counters).  A caller that splits a batch into token micro-batches and runs them on separate CUDA
+streams, one channel each (``nanovllm.layers.linear.tp_channel``), keeps one collective per channel
+in flight, so the wire time of one micro-batch hides under the GEMMs of the other.
 """
 from __future__ import annotations
 
@@ -55,13 +60,15 @@ class PeerAllReduce:
         self.tp_tokens = int(lib.ql_tp_max_tokens())
         self.tp_hidden = int(lib.ql_tp_max_hidden())
         self.push = os.environ.get("QL_TP_PUSH", "1") != "0"
+        self.channels = int(lib.ql_tp_channels()) if self.tp_tokens else 0
         self._bufs = {}
         if self.tp_tokens:
             dev = torch.device("cuda", torch.cuda.current_device())
             cap = self.tp_tokens * self.tp_hidden
-            for which, nbytes in ((0, cap * 2), (1, cap), (2, self.tp_tokens * 4)):
-                ptr = lib.ql_tp_buffer(which)
-                self._bufs[which] = torch.as_tensor(_DevMem(ptr, nbytes), device=dev)
+            for ch in range(self.channels):
+                for which, nbytes in ((0, cap * 2), (1, cap), (2, self.tp_tokens * 4)):
+                    ptr = lib.ql_tp_buffer(which, ch)
+                    self._bufs[ch, which] = torch.as_tensor(_DevMem(ptr, nbytes), device=dev)
 
     @classmethod
     def create(cls, max_bytes: int, tp_tokens: int, tp_hidden: int) -> "PeerAllReduce | None":
@@ -135,13 +142,13 @@ class PeerAllReduce:
         # token owners hold whole 256-token tiles; the buffers carry that rounding (allreduce.cu)
         return bool(self.tp_tokens) and 0 < M <= self.tp_tokens and N % 8 == 0 and 0 < N <= self.tp_hidden
 
-    def partial_view(self, M: int, N: int) -> torch.Tensor:
+    def partial_view(self, M: int, N: int, channel: int = 0) -> torch.Tensor:
         """bf16 [M, N] window of this rank's partial buffer: where a row-parallel GEMM writes when
         the owners pull."""
-        return self._bufs[0][: M * N * 2].view(torch.bfloat16).view(M, N)
+        return self._bufs[channel, 0][: M * N * 2].view(torch.bfloat16).view(M, N)
 
     @torch.no_grad()
-    def gemm_push(self, qx, sx, qw, sw, bias, dtype) -> None:
+    def gemm_push(self, qx, sx, qw, sw, bias, dtype, channel: int = 0) -> None:
         """ql_tp_gemm_push: row-parallel W8A8 GEMM whose epilogue delivers every 256-token tile to
         the rank that owns those tokens (GEMM + reduce-scatter in one kernel)."""
         assert qx.dtype == dtype and qw.dtype == dtype and qx.is_contiguous() and qw.is_contiguous()
@@ -150,23 +157,28 @@ class PeerAllReduce:
         assert K % 128 == 0 and self.fits_big(M, N)
         _ext._check(self.lib.ql_tp_gemm_push(qx.data_ptr(), sx.data_ptr(), qw.data_ptr(), sw.data_ptr(),
                                              None if bias is None else bias.data_ptr(), M, N, K,
-                                             _ext.fmt_of(dtype), torch.cuda.current_stream().cuda_stream))
+                                             _ext.fmt_of(dtype), channel,
+                                             torch.cuda.current_stream().cuda_stream))
 
     @torch.no_grad()
-    def reduce_quant_gather(self, M: int, N: int, dtype, pushed: bool):
-        """ql_tp_reduce_quant_gather -> (q [M, N], s [M]): views of the symmetric buffers, valid
-        until the next prefill-sized collective."""
-        _ext._check(self.lib.ql_tp_reduce_quant_gather(M, N, _ext.fmt_of(dtype), 1 if pushed else 0,
+    def reduce_quant_gather(self, M: int, N: int, dtype, pushed: bool, channel: int = 0):
+        """ql_tp_reduce_quant_gather -> (q [M, N], s [M]): views of the channel's symmetric
+        buffers, valid until the next prefill-sized collective on that channel."""
+        _ext._check(self.lib.ql_tp_reduce_quant_gather(M, N, _ext.fmt_of(dtype), 1 if pushed else 0, channel,
                                                        torch.cuda.current_stream().cuda_stream))
-        q = self._bufs[1][: M * N].view(dtype).view(M, N)
-        s = self._bufs[2][: M * 4].view(torch.float32)
+        q = self._bufs[channel, 1][: M * N].view(dtype).view(M, N)
+        s = self._bufs[channel, 2][: M * 4].view(torch.float32)
         return q, s
 
     @torch.no_grad()
-    def all_reduce_big(self, M: int, N: int, pushed: bool, device) -> torch.Tensor:
-        """ql_tp_allreduce_bf16 -> fresh bf16 [M, N] (dist.all_reduce semantics)."""
-        out = torch.empty((M, N), dtype=torch.bfloat16, device=device)
-        _ext._check(self.lib.ql_tp_allreduce_bf16(M, N, 1 if pushed else 0, out.data_ptr(), N,
+    def all_reduce_big(self, M: int, N: int, pushed: bool, device, channel: int = 0,
+                       out: torch.Tensor | None = None) -> torch.Tensor:
+        """ql_tp_allreduce_bf16 -> bf16 [M, N] (dist.all_reduce semantics), fresh unless ``out``
+        (row pitch ``out.stride(0)``) is given."""
+        if out is None:
+            out = torch.empty((M, N), dtype=torch.bfloat16, device=device)
+        assert out.dtype == torch.bfloat16 and out.shape == (M, N) and out.stride(1) == 1
+        _ext._check(self.lib.ql_tp_allreduce_bf16(M, N, 1 if pushed else 0, out.data_ptr(), out.stride(0), channel,
                                                   torch.cuda.current_stream().cuda_stream))
         return out
 

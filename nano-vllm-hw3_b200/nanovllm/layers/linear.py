@@ -17,12 +17,32 @@ bias on rank 0 only and all-reduces the bf16 partial sums, as linear.py:150-152)
 """
 from __future__ import annotations
 
+import contextlib
+
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
 from torch import nn
 
 from nanovllm import _ext
+
+
+_tp_channel = [0]
+
+
+@contextlib.contextmanager
+def tp_channel(channel: int):
+    """Route the prefill-sized NVLink collectives of the row-parallel linears called inside the
+    block through ``channel`` (0 .. ql_tp_channels()-1; independent buffers, flags and call counters,
+    include/qlinear_b200.h).  A caller that runs two token micro-batches on two CUDA streams gives
+    each its own channel; every rank must use the same channel for the same micro-batch."""
+    prev = _tp_channel[0]
+    _ext.load().ql_tp_set_concurrent(1)   # reduce kernels release their stream late from here on
+    _tp_channel[0] = int(channel)
+    try:
+        yield
+    finally:
+        _tp_channel[0] = prev
 
 
 def divide(numerator, denominator):
@@ -207,10 +227,10 @@ class RowParallelLinear(LinearBase):
                 qx, sx = x.q, x.s
             else:
                 qx, sx = _ext.quant_rows(x.reshape(-1, x.shape[-1]), self.qdtype)
-            comm.gemm_push(qx, sx, self.qw, self._sw_kernel, b, self.qdtype)
+            comm.gemm_push(qx, sx, self.qw, self._sw_kernel, b, self.qdtype, _tp_channel[0])
             return qx.shape[0], N, True
         M = x.q.shape[0] if hasattr(x, "q") else x.reshape(-1, x.shape[-1]).shape[0]
-        self._linear(x, bias, out=comm.partial_view(M, N))
+        self._linear(x, bias, out=comm.partial_view(M, N, _tp_channel[0]))
         return M, N, False
 
     def forward_quant(self, x):
@@ -228,7 +248,7 @@ class RowParallelLinear(LinearBase):
         N = self.qw.shape[0]
         if comm is not None and comm.fits_big(M, N) and not comm.fits(M * N):
             M, N, pushed = self._big_partial(comm, x, bias)
-            return QuantizedActivation(*comm.reduce_quant_gather(M, N, self.qdtype, pushed))
+            return QuantizedActivation(*comm.reduce_quant_gather(M, N, self.qdtype, pushed, _tp_channel[0]))
         y = self.forward(x)
         return QuantizedActivation(*_ext.quant_rows(y.reshape(-1, N), self.qdtype))
 
@@ -253,7 +273,7 @@ class RowParallelLinear(LinearBase):
                 # prefill-sized output: reduce-scatter (from the GEMM epilogue) + all-gather
                 M, N, pushed = self._big_partial(comm, x, bias)
                 dev = x.q.device if hasattr(x, "q") else x.device
-                return comm.all_reduce_big(M, N, pushed, dev).view(lead + [N])
+                return comm.all_reduce_big(M, N, pushed, dev, _tp_channel[0]).view(lead + [N])
         y = self._linear(x, bias)
         dist.all_reduce(y)                               # reference linear.py:150-152
         return y

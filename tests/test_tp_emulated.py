@@ -37,6 +37,7 @@ class Emu:
 
     def __init__(self, ext, world):
         self.ext, self.lib, self.world = ext, ext.load(), world
+        self.ch = 1 if world == 4 else 0          # the channels are independent copies: cover both
         self.lib.ql_ar_destroy()
         ext._check(self.lib.ql_ar_init_local(1 << 16, TOKENS, HIDDEN, world))
 
@@ -47,7 +48,7 @@ class Emu:
     def buf(self, rank, which, nbytes):
         from nanovllm._comm import _DevMem
         self.ext._check(self.lib.ql_tp_emu_set_rank(rank))
-        ptr = self.lib.ql_tp_buffer(which)
+        ptr = self.lib.ql_tp_buffer(which, self.ch)
         assert ptr
         return torch.as_tensor(_DevMem(ptr, nbytes), device="cuda")
 
@@ -91,7 +92,7 @@ def test_pull_reduce_quant_gather(ext, emu, dn, M, N):
         emu.buf(r, 0, M * N * 2).view(torch.bfloat16).view(M, N).copy_(parts[r])
     y, q, s = _expected(ext, parts, dtype)
     for rep in range(2):                                  # second call: the epoch counters advanced
-        ext._check(emu.lib.ql_tp_reduce_quant_gather(M, N, ext.fmt_of(dtype), 0, emu.stream()))
+        ext._check(emu.lib.ql_tp_reduce_quant_gather(M, N, ext.fmt_of(dtype), 0, emu.ch, emu.stream()))
         torch.cuda.synchronize()
         for r in range(W):
             qr = emu.buf(r, 1, M * N).view(dtype).view(M, N)
@@ -110,7 +111,7 @@ def test_pull_allreduce_bf16(ext, emu, M, N):
         emu.buf(r, 0, M * N * 2).view(torch.bfloat16).view(M, N).copy_(parts[r])
     y, _, _ = _expected(ext, parts, None)
     out = torch.full((W, M, N), 7.0, dtype=torch.bfloat16, device="cuda")
-    ext._check(emu.lib.ql_tp_allreduce_bf16(M, N, 0, out.data_ptr(), N, emu.stream()))
+    ext._check(emu.lib.ql_tp_allreduce_bf16(M, N, 0, out.data_ptr(), N, emu.ch, emu.stream()))
     torch.cuda.synchronize()
     for r in range(W):
         assert torch.equal(out[r], y), r
@@ -136,9 +137,9 @@ def test_push_gemm_reduce_quant_gather(ext, emu, dn, bias, M, N, K):
         ext._check(emu.lib.ql_tp_emu_set_rank(r))
         ext._check(emu.lib.ql_tp_gemm_push(qx.data_ptr(), sx.data_ptr(), qw.data_ptr(), sw.data_ptr(),
                                            None if b is None else b.data_ptr(), M, N, K, ext.fmt_of(dtype),
-                                           emu.stream()))
+                                           emu.ch, emu.stream()))
     y, q, s = _expected(ext, parts, dtype)
-    ext._check(emu.lib.ql_tp_reduce_quant_gather(M, N, ext.fmt_of(dtype), 1, emu.stream()))
+    ext._check(emu.lib.ql_tp_reduce_quant_gather(M, N, ext.fmt_of(dtype), 1, emu.ch, emu.stream()))
     torch.cuda.synchronize()
     for r in range(W):
         assert torch.equal(emu.buf(r, 2, M * 4).view(torch.float32), s), r
@@ -166,13 +167,13 @@ def test_push_allreduce_bf16_and_graph_replay(ext, emu):
         for r, (qx, sx, qw, sw) in enumerate(ops):
             ext._check(emu.lib.ql_tp_emu_set_rank(r))
             ext._check(emu.lib.ql_tp_gemm_push(qx.data_ptr(), sx.data_ptr(), qw.data_ptr(), sw.data_ptr(), None,
-                                               M, N, K, ext.fmt_of(dtype), emu.stream()))
-        ext._check(emu.lib.ql_tp_allreduce_bf16(M, N, 1, out.data_ptr(), N, emu.stream()))
+                                               M, N, K, ext.fmt_of(dtype), emu.ch, emu.stream()))
+        ext._check(emu.lib.ql_tp_allreduce_bf16(M, N, 1, out.data_ptr(), N, emu.ch, emu.stream()))
         for r, (qx, sx, qw, sw) in enumerate(ops):
             ext._check(emu.lib.ql_tp_emu_set_rank(r))
             ext._check(emu.lib.ql_tp_gemm_push(qx.data_ptr(), sx.data_ptr(), qw.data_ptr(), sw.data_ptr(), None,
-                                               M, N, K, ext.fmt_of(dtype), emu.stream()))
-        ext._check(emu.lib.ql_tp_reduce_quant_gather(M, N, ext.fmt_of(dtype), 1, emu.stream()))
+                                               M, N, K, ext.fmt_of(dtype), emu.ch, emu.stream()))
+        ext._check(emu.lib.ql_tp_reduce_quant_gather(M, N, ext.fmt_of(dtype), 1, emu.ch, emu.stream()))
 
     one_round()                                            # eager
     torch.cuda.synchronize()
@@ -199,10 +200,11 @@ def test_push_allreduce_bf16_and_graph_replay(ext, emu):
 def test_capacity_and_argument_checks(ext, emu):
     lib = emu.lib
     assert lib.ql_tp_max_tokens() == TOKENS and lib.ql_tp_max_hidden() == HIDDEN
-    assert lib.ql_tp_reduce_quant_gather(TOKENS + 1, 1024, 0, 0, None) == 5      # QL_ERR_WORKSPACE
-    assert lib.ql_tp_reduce_quant_gather(512, HIDDEN + 8, 0, 0, None) == 5
-    assert lib.ql_tp_reduce_quant_gather(512, 1020, 0, 0, None) == 2             # N % 8
-    assert lib.ql_tp_reduce_quant_gather(512, 1024, 9, 0, None) == 1             # bad format
-    assert lib.ql_tp_reduce_quant_gather(0, 1024, 0, 0, None) == 0               # empty: nothing to do
+    assert lib.ql_tp_reduce_quant_gather(TOKENS + 1, 1024, 0, 0, 0, None) == 5      # QL_ERR_WORKSPACE
+    assert lib.ql_tp_reduce_quant_gather(512, HIDDEN + 8, 0, 0, 0, None) == 5
+    assert lib.ql_tp_reduce_quant_gather(512, 1020, 0, 0, 0, None) == 2             # N % 8
+    assert lib.ql_tp_reduce_quant_gather(512, 1024, 9, 0, 0, None) == 1             # bad format
+    assert lib.ql_tp_reduce_quant_gather(0, 1024, 0, 0, 0, None) == 0               # empty: nothing to do
     assert lib.ql_tp_emu_set_rank(emu.world) == 2
+    assert lib.ql_tp_reduce_quant_gather(512, 1024, 0, 0, lib.ql_tp_channels(), None) == 2   # no such channel
     assert lib.ql_ar_allreduce_bf16(ctypes.c_void_p(16), ctypes.c_void_p(16), 8, None) == 5   # one-shot path is not emulated
