@@ -351,13 +351,16 @@ def tp_check(stack, T, dtype, rank, world):
 
 
 def decode_leg(stack, m, T, dtype, group, world, peaks, args, dist_on):
-    """The same stack at a decode-sized batch, CUDA-graph replay: HBM-bound (every weight byte is
-    streamed once per step), reported against the measured HBM peak."""
+    """The same stack at a decode-sized batch: HBM-bound (every weight byte is streamed once per
+    step), reported against the measured HBM peak.  Single GPU, per-row scales: the whole stack is
+    ONE persistent launch (ql_chain_run, csrc/decode_chain.cu); the per-linear launches
+    (CUDA-graph replay of ql_linear x 4 x layers) are timed beside it and must give the same
+    bits for INT8.  TP > 1 / per-group: per-linear launches only."""
     from nanovllm import _ext
     gx = torch.Generator(device="cuda").manual_seed(2)
     x = torch.randn(T, m["hidden"], generator=gx, device="cuda", dtype=torch.float32).to(torch.bfloat16)
     n0 = _ext.launch_count()
-    stack.forward(x)
+    y_ref = stack.forward(x)
     launches = _ext.launch_count() - n0
     if not args.no_graph:
         s = torch.cuda.Stream()
@@ -371,16 +374,41 @@ def decode_leg(stack, m, T, dtype, group, world, peaks, args, dist_on):
     else:
         def fn():
             stack.forward(x)
-    ms = time_steps(fn, max(args.steps, 10), max(args.warmup, 3), dist_on)
+    steps, warm = max(args.steps, 10), max(args.warmup, 3)
+    ms_lin = time_steps(fn, steps, warm, dist_on)
     shapes = layer_shapes(m, world)
     _, by_layer = flops_bytes(T, shapes, group)
     by = by_layer * m["layers"]
-    return {"tokens_per_step": T, "ms_per_step": ms, "value": T / (ms * 1e-3), "unit": "tokens/s",
-            "gpu_launches_per_step": int(launches), "bound": "hbm",
-            "algorithmic_bytes_per_step": by, "achieved_gbs": by / (ms * 1e-3) / 1e9,
-            "peak_gbs": peaks["hbm"], "frac": by / (ms * 1e-3) / 1e9 / peaks["hbm"],
-            "note": "whole step incl. quantisers and launch gaps, per rank; weights stream from HBM "
-                    "(the stack's distinct weights exceed L2)"}
+    out = {"tokens_per_step": T, "bound": "hbm", "algorithmic_bytes_per_step": by, "peak_gbs": peaks["hbm"],
+           "unit": "tokens/s",
+           "per_linear_launches": {"ms_per_step": ms_lin, "gpu_launches_per_step": int(launches),
+                                   "frac": by / (ms_lin * 1e-3) / 1e9 / peaks["hbm"],
+                                   "kernel": "skinny_kernel (tcgen05 cluster split-K), one launch per linear, "
+                                             "cuda graph replay"}}
+    ms, kern, n_launch = ms_lin, out["per_linear_launches"]["kernel"], int(launches)
+    if world == 1 and group == 0 and T <= 16 and os.environ.get("QL_NO_CHAIN", "0") != "1":
+        ops = []
+        for li, mods in enumerate(stack.layers):
+            for j, mod in enumerate(mods):
+                ops.append((mod.qw, mod._sw_kernel, mod.bias, x if (li == 0 and j == 0) else None))
+        chain = _ext.DecodeChain(ops, T, dtype)
+        y_chain = chain.run()
+        torch.cuda.synchronize()
+        same = bool(torch.equal(y_chain, y_ref))
+        if dtype == torch.int8:
+            assert same, "decode chain result differs from the per-linear path (INT8 must be bit-identical)"
+        ms_chain = time_steps(chain.run, steps, warm, dist_on)
+        out["chain"] = {"ms_per_step": ms_chain, "gpu_launches_per_step": 1,
+                        "frac": by / (ms_chain * 1e-3) / 1e9 / peaks["hbm"],
+                        "equals_per_linear_bits": same,
+                        "kernel": "decode_chain_kernel (persistent, one launch per step)"}
+        if ms_chain < ms:
+            ms, kern, n_launch = ms_chain, out["chain"]["kernel"], 1
+    out.update(ms_per_step=ms, value=T / (ms * 1e-3), gpu_launches_per_step=n_launch, kernel=kern,
+               achieved_gbs=by / (ms * 1e-3) / 1e9, frac=by / (ms * 1e-3) / 1e9 / peaks["hbm"],
+               note="whole step incl. activation quantisation, per rank; weights stream from HBM "
+                    "(the stack's distinct weights exceed L2); headline = the faster of the two launch forms")
+    return out
 
 
 # ------------------------------------------------------------------ CPU arm

@@ -64,6 +64,9 @@ SIGNATURES = {
     "ql_tp_reduce_quant_gather": (_c_int, [_c_i64, _c_i64, _c_int, _c_int, _c_int, _c_vp]),
     "ql_tp_allreduce_bf16": (_c_int, [_c_i64, _c_i64, _c_int, _c_vp, _c_i64, _c_int, _c_vp]),
     "ql_workspace_bytes": (_c_sz, [_c_i64, _c_i64]),
+    "ql_chain_workspace_bytes": (_c_sz, [_c_vp, _c_int, _c_i64]),
+    "ql_chain_prepare": (_c_int, [_c_vp, _c_int, _c_i64, _c_int, _c_i64, _c_vp, _c_sz, _c_vp, _c_vp]),
+    "ql_chain_run": (_c_int, [_c_vp, _c_vp, _c_vp]),
     "ql_linear_path": (ctypes.c_char_p, [_c_i64, _c_i64, _c_i64, _c_i64]),
 }
 
@@ -310,7 +313,7 @@ def gemv_w8a8(x, qw, sw, bias, dtype, group_size: int = 0):
     with _on_device(x):
         _check(load().ql_gemv_w8a8(_ptr(x2), x2.stride(0) if M > 1 else K, _ptr(qw), _ptr(sw),
                                    _ptr(bias), _ptr(y), N, M, N, K, fmt, group_size, _stream(x)))
-    return y.view(y_shape)
+    return y if y_shape is None else y.view(y_shape)
 
 
 @torch.no_grad()
@@ -357,6 +360,60 @@ def silu_mul_quant(gate_up, dtype=None, want_bf16: bool = False):
         _check(load().ql_silu_mul_quant(_ptr(gate_up), gate_up.stride(0) if M > 1 else 2 * I, M, I, fmt,
                                         _ptr(q), _ptr(s), _ptr(h), _stream(gate_up)))
     return q, s, h
+
+
+class _ChainOp(ctypes.Structure):
+    """ql_chain_op (include/qlinear_b200.h)."""
+    _fields_ = [("qw", _c_vp), ("sw", _c_vp), ("bias", _c_vp), ("x", _c_vp), ("y", _c_vp),
+                ("ldx", _c_i64), ("ldy", _c_i64), ("N", _c_i64), ("K", _c_i64)]
+
+
+class DecodeChain:
+    """ql_chain_*: a chain of per-row W8A8 linears at M <= 16 tokens in ONE persistent launch.
+
+    ``ops`` is a list of ``(qw, sw, bias, x)``: ``x`` is a bf16 [M, K] tensor (row stride free) or
+    None = "the first K columns of the previous op's output" (how o_proj / down_proj consume the
+    leading columns of qkv / gate_up in the bench stack, and every layer the previous layer's
+    output).  Outputs are allocated here (bf16 [M, N] each, ``self.outputs``) and stay valid for
+    the life of the object; ``run()`` launches on the current stream and is graph-capturable."""
+
+    def __init__(self, ops, M: int, dtype: torch.dtype):
+        fmt = fmt_of(dtype)
+        assert 0 < M <= 16 and len(ops) > 0
+        dev = ops[0][0].device
+        self.M, self.dtype, self.device = M, dtype, dev
+        self.outputs, self._keep = [], []
+        arr = (_ChainOp * len(ops))()
+        for i, (qw, sw, bias, x) in enumerate(ops):
+            assert qw.dtype == dtype and qw.dim() == 2 and qw.is_contiguous() and qw.is_cuda
+            N, K = qw.shape
+            assert K % 128 == 0, f"K({K}) must be multiple of BLK_K(128)"      # reference :328
+            assert sw.dtype == torch.float32 and sw.numel() == N and sw.is_contiguous()
+            if bias is not None:
+                assert bias.dtype == torch.bfloat16 and bias.numel() == N and bias.is_contiguous()
+            if x is not None:
+                assert x.dtype == torch.bfloat16 and x.dim() == 2 and x.shape == (M, K) and x.stride(1) == 1
+            else:
+                assert i > 0 and self.outputs[-1].shape[1] >= K
+            y = torch.empty((M, N), dtype=torch.bfloat16, device=dev)
+            self.outputs.append(y)
+            self._keep.append((qw, sw, bias, x))
+            arr[i] = _ChainOp(qw.data_ptr(), sw.data_ptr(), _ptr(bias), _ptr(x), y.data_ptr(),
+                              (x.stride(0) if M > 1 else K) if x is not None else 0, N, N, K)
+        lib = load()
+        with _on_device(qw):
+            nbytes = lib.ql_chain_workspace_bytes(ctypes.addressof(arr), len(ops), M)
+            if nbytes == 0:
+                raise RuntimeError("qlinear_b200: this chain is not supported (ql_chain_workspace_bytes == 0)")
+            self._ws = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+            self._plan = ctypes.create_string_buffer(128)
+            _check(lib.ql_chain_prepare(ctypes.addressof(arr), len(ops), M, fmt, 0, self._ws.data_ptr(), nbytes,
+                                        ctypes.addressof(self._plan), _stream(qw)))
+
+    def run(self):
+        with _on_device(self._ws):
+            _check(load().ql_chain_run(ctypes.addressof(self._plan), self._ws.data_ptr(), _stream(self._ws)))
+        return self.outputs[-1]
 
 
 def launch_count() -> int:
