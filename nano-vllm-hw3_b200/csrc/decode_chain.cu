@@ -40,12 +40,17 @@ namespace ql {
 
 constexpr int kDcConsumers = 256;              // 8 MMA warps
 constexpr int kDcThreads = kDcConsumers + 32;  // + 1 producer warp
-constexpr int kDcMaxSlice = 2048;              // bytes of K per unit
-constexpr int kDcStageBytes = 8 * (kDcMaxSlice + 64);
-constexpr int kDcStages = 12;
-constexpr int kDcRedBytes = 2 * 8 * 128 * 4;   // double-buffered cross-warp reduction tile
-constexpr int kDcSmem = kDcStages * kDcStageBytes + kDcRedBytes + 1024 + 128;
-constexpr uint32_t kDcMagic = 0x51444331u;     // "QDC1"
+constexpr int kDcMaxSlice = 4096;              // bytes of K per unit: 32 pieces of 128 B, 4 per warp
+constexpr int kDcPieces = kDcMaxSlice / 128 / 8;   // pieces per warp
+constexpr int kDcSlotK = 1024;                 // bytes of K per ring slot (8 weight rows x <= 1 KB)
+constexpr int kDcSlotPitch = kDcSlotK + 64;    // rows 64 B apart modulo 128: conflict-free LDS.128
+constexpr int kDcSlotBytes = 8 * kDcSlotPitch;
+constexpr int kDcSlots = 22;                   // ~187 KB of weights in flight per SM
+constexpr int kDcR = 4;                        // row groups accumulated between cross-warp reductions
+constexpr int kDcRedBytes = 2 * 8 * kDcR * 128 * 4;   // double-buffered [8 warps][R][16 x 8] partial tiles
+constexpr int kDcSmem = kDcSlots * kDcSlotBytes + kDcRedBytes + 1024 + 128;
+constexpr uint32_t kDcMagic = 0x51444332u;     // "QDC2"
+static_assert(kDcSmem <= 227 * 1024, "decode chain shared memory");
 
 struct ChainOp {            // device-side descriptor, 128 bytes
   const uint8_t* qw;        // [N, K] codes
@@ -56,7 +61,7 @@ struct ChainOp {            // device-side descriptor, 128 bytes
   int64_t ldx, ldy;
   int N, K;
   int KS, RB;               // K slices x row blocks = units (<= grid)
-  int ksz, pitch;           // bytes of K per slice; shared-memory row pitch
+  int ksz, rot;             // bytes of K per slice; unit -> CTA rotation
   int RG;                   // groups of 8 weight rows
   int amax_cols;            // leading columns of y folded into the next op's amax (0: none)
   int x_amax;               // 1: amax[op] was produced by the previous op's epilogue
@@ -109,7 +114,6 @@ __device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
-__device__ __forceinline__ void finalizer_sync() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
 
 // 16 bf16 (two 16-byte vectors) -> 16 codes (4 words)
 template <int FMT>
@@ -118,53 +122,70 @@ __device__ __forceinline__ void quant16(const uint4& v0, const uint4& v1, float 
   w[0] = q0.x; w[1] = q0.y; w[2] = q1.x; w[3] = q1.y;
 }
 
+// unit of CTA `cta` in an op: row block rb, K slice ks (false: the CTA idles through this op)
+__device__ __forceinline__ bool dc_unit(int cta, int G, int rot, int KS, int RB, int& rb, int& ks) {
+  int v = cta + rot;
+  if (v >= G) v -= G;
+  rb = ks = 0;
+  if (v >= KS * RB) return false;
+  rb = v / KS;
+  ks = v - rb * KS;
+  return true;
+}
+
 template <int FMT>
 __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const ChainParams p) {
   using acc_t = typename std::conditional<FMT == QL_INT8, int, float>::type;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
   uint8_t* ring = smem;
-  uint32_t* red = reinterpret_cast<uint32_t*>(ring + kDcStages * kDcStageBytes);   // [2][8][128]
+  uint32_t* red = reinterpret_cast<uint32_t*>(ring + kDcSlots * kDcSlotBytes);   // [2][8][R][128]
   uint8_t* small = reinterpret_cast<uint8_t*>(red) + kDcRedBytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(small);
-  uint64_t* empty_bar = full_bar + kDcStages;
-  float* sx_s = reinterpret_cast<float*>(small + 256);     // [16]
-  int* amax_s = reinterpret_cast<int*>(small + 320);       // [16]
-  uint32_t* flag_s = reinterpret_cast<uint32_t*>(small + 384);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(small);                       // [kDcSlots]
+  uint64_t* empty_bar = full_bar + kDcSlots;                                     // [kDcSlots] (352 B so far)
+  float* sx_s = reinterpret_cast<float*>(small + 384);     // [16]
+  int* amax_s = reinterpret_cast<int*>(small + 448);       // [16]
+  uint32_t* flag_s = reinterpret_cast<uint32_t*>(small + 512);
+  ChainOp* desc_s = reinterpret_cast<ChainOp*>(small + 640);   // [2]: this op's / the next op's descriptor
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int G = gridDim.x, cta = blockIdx.x;
   constexpr float qmax = Fmt<FMT>::qmax;
 
   if (tid == 0) {
-    for (int i = 0; i < kDcStages; ++i) {
+    for (int i = 0; i < kDcSlots; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 8);
     }
     mbar_fence_init();
   }
+  if (tid < 8) reinterpret_cast<uint4*>(desc_s)[tid] = __ldg(reinterpret_cast<const uint4*>(p.ops) + tid);
   __syncthreads();
 
   if (warp == 8) {
     // ===================== producer: every op's weights, as far ahead as the ring allows ==========
-    int stage = 0;
+    int slot = 0;
     uint32_t phase = 0;
     for (int l = 0; l < p.n_ops; ++l) {
       const ChainOp& op = p.ops[l];
       const int KS = __ldg(&op.KS), RB = __ldg(&op.RB);
-      if (cta >= KS * RB) continue;
-      const int rb = cta / KS, ks = cta - rb * KS;
-      const int RG = __ldg(&op.RG), ksz = __ldg(&op.ksz), pitch = __ldg(&op.pitch), K = __ldg(&op.K);
+      int rb, ks;
+      if (!dc_unit(cta, G, __ldg(&op.rot), KS, RB, rb, ks)) continue;
+      const int RG = __ldg(&op.RG), ksz = __ldg(&op.ksz), K = __ldg(&op.K);
       const int rg0 = (int)((int64_t)rb * RG / RB), rg1 = (int)((int64_t)(rb + 1) * RG / RB);
       const uint8_t* src0 = op.qw + (size_t)ks * ksz;
       for (int rg = rg0; rg < rg1; ++rg) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        if (lane == 0) mbar_expect_tx(&full_bar[stage], 8u * (uint32_t)ksz);
-        __syncwarp();
-        if (lane < 8)
-          bulk_load(ring + stage * kDcStageBytes + lane * pitch, src0 + (size_t)(rg * 8 + lane) * K,
-                    (uint32_t)ksz, &full_bar[stage], kEvictFirst);
-        if (++stage == kDcStages) { stage = 0; phase ^= 1; }
+        const uint8_t* srow = src0 + (size_t)(rg * 8 + (lane & 7)) * K;
+        for (int off = 0; off < ksz; off += kDcSlotK) {
+          const uint32_t bytes = (uint32_t)(ksz - off < kDcSlotK ? ksz - off : kDcSlotK);
+          mbar_wait(&empty_bar[slot], phase ^ 1);
+          if (lane == 0) mbar_expect_tx(&full_bar[slot], 8u * bytes);
+          __syncwarp();
+          if (lane < 8)
+            bulk_load(ring + slot * kDcSlotBytes + lane * kDcSlotPitch, srow + off, bytes, &full_bar[slot],
+                      kEvictFirst);
+          if (++slot == kDcSlots) { slot = 0; phase ^= 1; }
+        }
       }
     }
     return;
@@ -172,36 +193,57 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
 
   // ===================== consumers =====================
   const int g = lane >> 2, t = lane & 3;     // mma fragment coordinates
-  const int e_m = tid >> 3, e_j = tid & 7;   // finalizer coordinates (threads 0..127): token, row in group
-  int stage = 0;
+  const int e_m = (tid & 127) >> 3, e_j = tid & 7, e_r = tid >> 7;   // finalizer: token, row in group, group parity
+  int slot = 0;
   uint32_t phase = 0;
   uint32_t red_buf = 0;
 
   for (int l = 0; l < p.n_ops; ++l) {
-    const ChainOp& op = p.ops[l];
-    const int KS = __ldg(&op.KS), RB = __ldg(&op.RB);
-    const bool active = cta < KS * RB;
+    const ChainOp& op = desc_s[l & 1];
+    const int KS = op.KS, RB = op.RB;
+    int rb, ks;
+    const bool active = dc_unit(cta, G, op.rot, KS, RB, rb, ks);
     if (active) {
-      const int rb = cta / KS, ks = cta - rb * KS;
-      const int RG = __ldg(&op.RG), ksz = __ldg(&op.ksz), pitch = __ldg(&op.pitch), N = __ldg(&op.N);
+      const int RG = op.RG, ksz = op.ksz, N = op.N;
       const int rg0 = (int)((int64_t)rb * RG / RB), rg1 = (int)((int64_t)(rb + 1) * RG / RB);
       const int nsc = ksz >> 7;                          // 128-byte pieces of the K slice
+      const int nslot = (ksz + kDcSlotK - 1) / kDcSlotK;
       const int64_t ldx = op.ldx, ldy = op.ldy;
       const uint16_t* xk = op.x + (size_t)ks * ksz;      // this slice's first column
       const float* sw = op.sw;
       const uint16_t* bias = op.bias;
       uint16_t* y = op.y;
-      const int amax_cols = __ldg(&op.amax_cols);
+      const int amax_cols = op.amax_cols;
+
+      // ---- this warp's raw activation pieces (L2): in flight together with the amax read --------
+      uint4 xv[kDcPieces][2][2][2];                      // [piece][half][token g / g+8][vector]
+#pragma unroll
+      for (int i = 0; i < kDcPieces; ++i) {
+        const int sc = warp + 8 * i;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int kb = sc * 128 + h * 64 + t * 16;
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const int m = g + 8 * u;
+            xv[i][h][u][0] = xv[i][h][u][1] = make_uint4(0, 0, 0, 0);
+            if (sc < nsc && m < p.M) {
+              const uint4* s = reinterpret_cast<const uint4*>(xk + (size_t)m * ldx + kb);
+              xv[i][h][u][0] = __ldcg(s);
+              xv[i][h][u][1] = __ldcg(s + 1);
+            }
+          }
+        }
+      }
 
       // ---- per-token scale of the input rows ------------------------------------------------
-      if (__ldg(&op.x_amax)) {
+      if (op.x_amax) {
         if (tid < 16) amax_s[tid] = (int)__ldcg(p.amax + l * 16 + tid);
       } else {
         // no producer in the chain: every CTA scans the (small) activation once
         if (tid < 16) amax_s[tid] = 0;
         consumer_sync();
-        const int K = __ldg(&op.K);
-        const int nvec = K >> 3;
+        const int nvec = op.K >> 3;
         for (int m = warp; m < p.M; m += 8) {
           float a = 0.0f;
           const uint4* row = reinterpret_cast<const uint4*>(op.x + (size_t)m * ldx);
@@ -216,96 +258,101 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
       const float inv_lo = __fdiv_rn(qmax, am_lo), inv_hi = __fdiv_rn(qmax, am_hi);
       if (tid < 16) sx_s[tid] = __fdiv_rn(fmaxf(__int_as_float(amax_s[tid]), 1e-8f), qmax);
 
-      // ---- this warp's activation fragments: pieces warp, warp + 8 of the slice ---------------
-      uint32_t a_lo[2][2][4], a_hi[2][2][4];
+      // ---- quantise into mma A fragments (Triton quantiser arithmetic :26-41) ------------------
+      uint32_t a_lo[kDcPieces][2][4], a_hi[kDcPieces][2][4];
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int sc = warp + 8 * i;
+      for (int i = 0; i < kDcPieces; ++i)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-          const int kb = sc * 128 + h * 64 + t * 16;
-          uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0, u0 = v0, u1 = v0;
-          if (sc < nsc) {
-            if (g < p.M) {
-              const uint4* s = reinterpret_cast<const uint4*>(xk + (size_t)g * ldx + kb);
-              v0 = __ldcg(s); v1 = __ldcg(s + 1);
-            }
-            if (g + 8 < p.M) {
-              const uint4* s = reinterpret_cast<const uint4*>(xk + (size_t)(g + 8) * ldx + kb);
-              u0 = __ldcg(s); u1 = __ldcg(s + 1);
-            }
-          }
-          quant16<FMT>(v0, v1, inv_lo, a_lo[i][h]);
-          quant16<FMT>(u0, u1, inv_hi, a_hi[i][h]);
+          quant16<FMT>(xv[i][h][0][0], xv[i][h][0][1], inv_lo, a_lo[i][h]);
+          quant16<FMT>(xv[i][h][1][0], xv[i][h][1][1], inv_hi, a_hi[i][h]);
         }
-      }
 
-      // ---- stream the unit's weight row groups --------------------------------------------------
+      // ---- stream the unit's weight row groups, kDcR at a time ----------------------------------
       float run_max = 0.0f;
-      float sw_next = 0.0f, b_next = 0.0f;
-      if (tid < 128) {
-        const int n = rg0 * 8 + e_j;
-        sw_next = __ldg(sw + n);
-        b_next = bias != nullptr ? bf16_lo(__ldg(bias + n)) : 0.0f;
-      }
-      for (int rg = rg0; rg < rg1; ++rg) {
-        const float sw_cur = sw_next, b_cur = b_next;
-        if (tid < 128 && rg + 1 < rg1) {
-          const int n = (rg + 1) * 8 + e_j;
-          sw_next = __ldg(sw + n);
-          b_next = bias != nullptr ? bf16_lo(__ldg(bias + n)) : 0.0f;
+      for (int rgb = rg0; rgb < rg1; rgb += kDcR) {
+        const int nr = rg1 - rgb < kDcR ? rg1 - rgb : kDcR;
+        // scales / bias of the rows this thread finalises (static data: the loads overlap the MMAs)
+        float swv[kDcR / 2], bv[kDcR / 2];
+#pragma unroll
+        for (int j = 0; j < kDcR / 2; ++j) {
+          const int r = e_r + 2 * j;
+          const int n = (rgb + r) * 8 + e_j;
+          const bool ok = r < nr && KS == 1;
+          swv[j] = ok ? __ldg(sw + n) : 0.0f;
+          bv[j] = (ok && bias != nullptr) ? bf16_lo(__ldg(bias + n)) : 0.0f;
         }
-        acc_t c[4] = {0, 0, 0, 0};
-        mbar_wait(&full_bar[stage], phase);
-        const uint8_t* wrow = ring + stage * kDcStageBytes + g * pitch + t * 16;
+        acc_t c[kDcR][4];
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int sc = warp + 8 * i;
-          if (sc < nsc) {
+        for (int r = 0; r < kDcR; ++r) c[r][0] = c[r][1] = c[r][2] = c[r][3] = 0;
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              const uint4 w = *reinterpret_cast<const uint4*>(wrow + sc * 128 + h * 64);
-              if constexpr (FMT == QL_INT8) {
-                mma_i8_sync(c, a_lo[i][h][0], a_hi[i][h][0], a_lo[i][h][1], a_hi[i][h][1], w.x, w.y);
-                mma_i8_sync(c, a_lo[i][h][2], a_hi[i][h][2], a_lo[i][h][3], a_hi[i][h][3], w.z, w.w);
-              } else {
-                mma_f8_sync(c, a_lo[i][h][0], a_hi[i][h][0], a_lo[i][h][1], a_hi[i][h][1], w.x, w.y);
-                mma_f8_sync(c, a_lo[i][h][2], a_hi[i][h][2], a_lo[i][h][3], a_hi[i][h][3], w.z, w.w);
+        for (int r = 0; r < kDcR; ++r) {
+          if (r < nr) {
+#pragma unroll
+            for (int i = 0; i < kDcPieces; ++i) {
+              if (i < nslot) {
+                mbar_wait(&full_bar[slot], phase);
+                if (warp + 8 * i < nsc) {
+                  const uint8_t* wrow = ring + slot * kDcSlotBytes + g * kDcSlotPitch + warp * 128 + t * 16;
+#pragma unroll
+                  for (int h = 0; h < 2; ++h) {
+                    const uint4 w = *reinterpret_cast<const uint4*>(wrow + h * 64);
+                    if constexpr (FMT == QL_INT8) {
+                      mma_i8_sync(c[r], a_lo[i][h][0], a_hi[i][h][0], a_lo[i][h][1], a_hi[i][h][1], w.x, w.y);
+                      mma_i8_sync(c[r], a_lo[i][h][2], a_hi[i][h][2], a_lo[i][h][3], a_hi[i][h][3], w.z, w.w);
+                    } else {
+                      mma_f8_sync(c[r], a_lo[i][h][0], a_hi[i][h][0], a_lo[i][h][1], a_hi[i][h][1], w.x, w.y);
+                      mma_f8_sync(c[r], a_lo[i][h][2], a_hi[i][h][2], a_lo[i][h][3], a_hi[i][h][3], w.z, w.w);
+                    }
+                  }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty_bar[slot]);
+                if (++slot == kDcSlots) { slot = 0; phase ^= 1; }
               }
             }
           }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty_bar[stage]);
-        if (++stage == kDcStages) { stage = 0; phase ^= 1; }
 
-        // cross-warp reduction of the 16 x 8 tile (every warp holds a K piece of it)
-        uint32_t* rt = red + red_buf * 1024 + warp * 128;
-        uint32_t cu[4];
-        if constexpr (FMT == QL_INT8) { cu[0] = c[0]; cu[1] = c[1]; cu[2] = c[2]; cu[3] = c[3]; }
-        else { cu[0] = __float_as_uint(c[0]); cu[1] = __float_as_uint(c[1]); cu[2] = __float_as_uint(c[2]); cu[3] = __float_as_uint(c[3]); }
-        *reinterpret_cast<uint2*>(rt + g * 8 + 2 * t) = make_uint2(cu[0], cu[1]);
-        *reinterpret_cast<uint2*>(rt + (g + 8) * 8 + 2 * t) = make_uint2(cu[2], cu[3]);
-        consumer_sync();
-        if (tid < 128) {
-          const uint32_t* rs = red + red_buf * 1024 + tid;
-          uint32_t sum = rs[0];
+        // cross-warp reduction of the nr 16 x 8 tiles (every warp holds a K piece of each)
+        uint32_t* rt = red + red_buf * (8 * kDcR * 128) + warp * (kDcR * 128);
 #pragma unroll
-          for (int w = 1; w < 8; ++w) {
-            if constexpr (FMT == QL_INT8) sum = (uint32_t)((int)sum + (int)rs[w * 128]);
-            else sum = __float_as_uint(__fadd_rn(__uint_as_float(sum), __uint_as_float(rs[w * 128])));
+        for (int r = 0; r < kDcR; ++r) {
+          if (r < nr) {
+            uint32_t cu[4];
+            if constexpr (FMT == QL_INT8) { cu[0] = c[r][0]; cu[1] = c[r][1]; cu[2] = c[r][2]; cu[3] = c[r][3]; }
+            else {
+              cu[0] = __float_as_uint(c[r][0]); cu[1] = __float_as_uint(c[r][1]);
+              cu[2] = __float_as_uint(c[r][2]); cu[3] = __float_as_uint(c[r][3]);
+            }
+            *reinterpret_cast<uint2*>(rt + r * 128 + g * 8 + 2 * t) = make_uint2(cu[0], cu[1]);
+            *reinterpret_cast<uint2*>(rt + r * 128 + (g + 8) * 8 + 2 * t) = make_uint2(cu[2], cu[3]);
           }
-          const int n = rg * 8 + e_j;
-          if (e_m < p.M) {
-            if (KS == 1) {
-              const float a = FMT == QL_INT8 ? __int2float_rn((int)sum) : __uint_as_float(sum);
-              float v = __fmul_rn(__fmul_rn(a, sx_s[e_m]), sw_cur);     // (acc * sa) * sb, reference :121
-              if (bias != nullptr) v = __fadd_rn(v, b_cur);
-              const uint16_t o = f2bf(v);
-              y[(size_t)e_m * ldy + n] = o;
-              if (n < amax_cols) run_max = fmaxf(run_max, fabsf(bf16_lo(o)));
-            } else {
-              p.part[((size_t)ks * 16 + e_m) * N + n] = sum;
+        }
+        consumer_sync();
+#pragma unroll
+        for (int j = 0; j < kDcR / 2; ++j) {
+          const int r = e_r + 2 * j;
+          if (r < nr) {
+            const uint32_t* rs = red + red_buf * (8 * kDcR * 128) + r * 128 + (tid & 127);
+            uint32_t sum = rs[0];
+#pragma unroll
+            for (int w = 1; w < 8; ++w) {
+              if constexpr (FMT == QL_INT8) sum = (uint32_t)((int)sum + (int)rs[w * (kDcR * 128)]);
+              else sum = __float_as_uint(__fadd_rn(__uint_as_float(sum), __uint_as_float(rs[w * (kDcR * 128)])));
+            }
+            const int n = (rgb + r) * 8 + e_j;
+            if (e_m < p.M) {
+              if (KS == 1) {
+                const float a = FMT == QL_INT8 ? __int2float_rn((int)sum) : __uint_as_float(sum);
+                float v = __fmul_rn(__fmul_rn(a, sx_s[e_m]), swv[j]);     // (acc * sa) * sb, reference :121
+                if (bias != nullptr) v = __fadd_rn(v, bv[j]);
+                const uint16_t o = f2bf(v);
+                y[(size_t)e_m * ldy + n] = o;
+                if (n < amax_cols) run_max = fmaxf(run_max, fabsf(bf16_lo(o)));
+              } else {
+                p.part[((size_t)ks * 16 + e_m) * N + n] = sum;
+              }
             }
           }
         }
@@ -313,22 +360,22 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
       }
 
       // ---- K-slice partials: the last slice to arrive finishes the row block --------------------
-      if (KS > 1 && tid < 128) {
+      if (KS > 1) {
         __threadfence();
-        finalizer_sync();
+        consumer_sync();
         if (tid == 0) {
-          uint32_t* ctr = p.blk_ctr + __ldg(&op.ctr_off) + rb;
+          uint32_t* ctr = p.blk_ctr + op.ctr_off + rb;
           const uint32_t old = atomicAdd(ctr, 1u);
           const uint32_t last = old == (uint32_t)(KS - 1);
           if (last) *ctr = 0;                              // ready for the next launch
           *flag_s = last;
         }
-        finalizer_sync();
+        consumer_sync();
         if (*flag_s) {
           __threadfence();
           if (e_m < p.M) {
             const float sxm = sx_s[e_m];
-            for (int rg = rg0; rg < rg1; ++rg) {
+            for (int rg = rg0 + e_r; rg < rg1; rg += 2) {
               const int n = rg * 8 + e_j;
               const uint32_t* src = p.part + (size_t)e_m * N + n;
               uint32_t sum = __ldcg(src);
@@ -349,18 +396,22 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
       }
 
       // ---- fold |y| into the next op's per-token amax --------------------------------------------
-      if (tid < 128 && amax_cols > 0) {
+      if (amax_cols > 0) {
         run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 1));
         run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 2));
         run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 4));
         if (e_j == 0 && e_m < p.M && run_max > 0.0f)
           atomicMax(reinterpret_cast<int*>(p.amax) + (l + 1) * 16 + e_m, __float_as_int(run_max));
       }
-      if (tid < 128) __threadfence();
+      __threadfence();
     }
 
     // ---- grid barrier: op l is complete everywhere (its output and the next amax are visible) ----
     if (l + 1 < p.n_ops) {
+      // the next op's descriptor is static: fetch it while the barrier is in flight
+      if (tid >= 32 && tid < 40)
+        reinterpret_cast<uint4*>(desc_s + ((l + 1) & 1))[tid - 32] =
+            __ldg(reinterpret_cast<const uint4*>(p.ops + l + 1) + (tid - 32));
       consumer_sync();
       if (tid == 0) {
         red_release_gpu_add(p.sync, 1u);
@@ -444,7 +495,7 @@ static int plan_chain(const ql_chain_op* ops, int n_ops, int64_t M, int grid, Ch
       d.KS = KS;
       d.RB = RB;
       d.ksz = (int)(o.K / KS);
-      d.pitch = d.ksz + 64;                 // ksz % 128 == 0: rows 64 B apart modulo 128 -> conflict-free LDS.128
+      d.rot = (int)(((int64_t)l * 41) % grid);   // spread the idle / one-group-longer units over the SMs
       d.RG = RG;
       d.x_amax = chained ? 1 : 0;
       d.amax_cols = (l + 1 < n_ops && ops[l + 1].x == nullptr) ? (int)ops[l + 1].K : 0;
