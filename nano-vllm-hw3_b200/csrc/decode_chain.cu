@@ -77,7 +77,25 @@ struct ChainParams {
   uint32_t* amax;           // [n_ops][16] float bit patterns
   uint32_t* blk_ctr;
   uint32_t* part;           // K-slice partials [KS][16][N] (int32 / fp32 bits)
+  long long* trace;         // debug (ql_debug_set_trace): clock64 stamps [cta][16 ops][16], else nullptr
+  int flags;                // debug (QL_CHAIN_DEBUG): skip parts of the kernel for attribution -- WRONG RESULTS
 };
+#define DC_TRACE(i)                                                                          \
+  do {                                                                                       \
+    if (p.trace != nullptr && tid == 0 && l < 16)                                            \
+      p.trace[((size_t)cta * 16 + l) * 16 + (i)] = clock64();                                \
+  } while (0)
+
+// mbarrier wait without the globaltimer watchdog of mbar_wait (flag 64: attribution experiment)
+__device__ __forceinline__ void dc_wait(uint64_t* bar, uint32_t parity, int flags) {
+  if (flags & 64) {
+    uint32_t n = 0;
+    while (!mbar_try_wait(bar, parity))
+      if (++n > (1u << 28)) __trap();
+  } else {
+    mbar_wait(bar, parity);
+  }
+}
 
 __device__ __forceinline__ void mma_i8_sync(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                             uint32_t b0, uint32_t b1) {
@@ -178,7 +196,12 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
         const uint8_t* srow = src0 + (size_t)(rg * 8 + (lane & 7)) * K;
         for (int off = 0; off < ksz; off += kDcSlotK) {
           const uint32_t bytes = (uint32_t)(ksz - off < kDcSlotK ? ksz - off : kDcSlotK);
-          mbar_wait(&empty_bar[slot], phase ^ 1);
+          dc_wait(&empty_bar[slot], phase ^ 1, p.flags);
+          if (p.flags & 8) {
+            if (lane == 0) mbar_arrive(&full_bar[slot]);
+            if (++slot == kDcSlots) { slot = 0; phase ^= 1; }
+            continue;
+          }
           if (lane == 0) mbar_expect_tx(&full_bar[slot], 8u * bytes);
           __syncwarp();
           if (lane < 8)
@@ -203,6 +226,7 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
     const int KS = op.KS, RB = op.RB;
     int rb, ks;
     const bool active = dc_unit(cta, G, op.rot, KS, RB, rb, ks);
+    DC_TRACE(0);
     if (active) {
       const int RG = op.RG, ksz = op.ksz, N = op.N;
       const int rg0 = (int)((int64_t)rb * RG / RB), rg1 = (int)((int64_t)(rb + 1) * RG / RB);
@@ -227,7 +251,7 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
           for (int u = 0; u < 2; ++u) {
             const int m = g + 8 * u;
             xv[i][h][u][0] = xv[i][h][u][1] = make_uint4(0, 0, 0, 0);
-            if (sc < nsc && m < p.M) {
+            if (sc < nsc && m < p.M && !(p.flags & 16)) {
               const uint4* s = reinterpret_cast<const uint4*>(xk + (size_t)m * ldx + kb);
               xv[i][h][u][0] = __ldcg(s);
               xv[i][h][u][1] = __ldcg(s + 1);
@@ -253,6 +277,7 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
         }
       }
       consumer_sync();
+      DC_TRACE(1);
       const float am_lo = fmaxf(__int_as_float(amax_s[g]), 1e-8f);
       const float am_hi = fmaxf(__int_as_float(amax_s[g + 8]), 1e-8f);
       const float inv_lo = __fdiv_rn(qmax, am_lo), inv_hi = __fdiv_rn(qmax, am_hi);
@@ -270,6 +295,7 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
 
       // ---- stream the unit's weight row groups, kDcR at a time ----------------------------------
       float run_max = 0.0f;
+      if (p.trace != nullptr && tid == 0 && l < 16 && (a_lo[0][0][0] ^ a_hi[0][0][0]) != 0x12345678u) DC_TRACE(2);
       for (int rgb = rg0; rgb < rg1; rgb += kDcR) {
         const int nr = rg1 - rgb < kDcR ? rg1 - rgb : kDcR;
         // scales / bias of the rows this thread finalises (static data: the loads overlap the MMAs)
@@ -291,8 +317,9 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
 #pragma unroll
             for (int i = 0; i < kDcPieces; ++i) {
               if (i < nslot) {
-                mbar_wait(&full_bar[slot], phase);
-                if (warp + 8 * i < nsc) {
+                dc_wait(&full_bar[slot], phase, p.flags);
+                if (r == 0 && i == 0 && rgb == rg0) DC_TRACE(3);
+                if (warp + 8 * i < nsc && !(p.flags & 1)) {
                   const uint8_t* wrow = ring + slot * kDcSlotBytes + g * kDcSlotPitch + warp * 128 + t * 16;
 #pragma unroll
                   for (int h = 0; h < 2; ++h) {
@@ -308,12 +335,15 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&empty_bar[slot]);
+                if (r == 0 && i == 0 && rgb == rg0) DC_TRACE(4);
                 if (++slot == kDcSlots) { slot = 0; phase ^= 1; }
               }
             }
+            if (r == 0 && rgb == rg0) DC_TRACE(5);
           }
         }
 
+        if (rgb == rg0) DC_TRACE(6);
         // cross-warp reduction of the nr 16 x 8 tiles (every warp holds a K piece of each)
         uint32_t* rt = red + red_buf * (8 * kDcR * 128) + warp * (kDcR * 128);
 #pragma unroll
@@ -330,6 +360,7 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
           }
         }
         consumer_sync();
+        if (rgb == rg0) DC_TRACE(7);
 #pragma unroll
         for (int j = 0; j < kDcR / 2; ++j) {
           const int r = e_r + 2 * j;
@@ -356,9 +387,11 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
             }
           }
         }
+        if (rgb == rg0) DC_TRACE(8);
         red_buf ^= 1;
       }
 
+      DC_TRACE(9);
       // ---- K-slice partials: the last slice to arrive finishes the row block --------------------
       if (KS > 1) {
         __threadfence();
@@ -400,10 +433,11 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
         run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 1));
         run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 2));
         run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 4));
-        if (e_j == 0 && e_m < p.M && run_max > 0.0f)
+        if (e_j == 0 && e_m < p.M && run_max > 0.0f && !(p.flags & 4))
           atomicMax(reinterpret_cast<int*>(p.amax) + (l + 1) * 16 + e_m, __float_as_int(run_max));
       }
-      __threadfence();
+      if (!(p.flags & 32)) __threadfence();
+      DC_TRACE(10);
     }
 
     // ---- grid barrier: op l is complete everywhere (its output and the next amax are visible) ----
@@ -413,14 +447,23 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
         reinterpret_cast<uint4*>(desc_s + ((l + 1) & 1))[tid - 32] =
             __ldg(reinterpret_cast<const uint4*>(p.ops + l + 1) + (tid - 32));
       consumer_sync();
+      DC_TRACE(11);
       if (tid == 0) {
         red_release_gpu_add(p.sync, 1u);
-        const uint32_t target = (uint32_t)(l + 1) * (uint32_t)G;
+        DC_TRACE(12);
+        const uint32_t target = (p.flags & 2) ? 0u : (uint32_t)(l + 1) * (uint32_t)G;
         if (ld_acquire_gpu(p.sync) < target) {
-          const uint64_t t0 = globaltimer_ns();
-          while (ld_acquire_gpu(p.sync) < target)
-            if (globaltimer_ns() - t0 > 4000000000ull) __trap();   // 4 s: never hang the GPU
+          if (p.flags & 64) {
+            uint32_t n = 0;
+            while (ld_acquire_gpu(p.sync) < target)
+              if (++n > (1u << 26)) __trap();
+          } else {
+            const uint64_t t0 = globaltimer_ns();
+            while (ld_acquire_gpu(p.sync) < target)
+              if (globaltimer_ns() - t0 > 4000000000ull) __trap();   // 4 s: never hang the GPU
+          }
         }
+        DC_TRACE(13);
       }
       consumer_sync();
     }
@@ -578,6 +621,11 @@ int ql_chain_run(const ql_chain_plan* plan, void* workspace, ql_stream_t stream)
   p.amax = reinterpret_cast<uint32_t*>(ws + pl.off_amax);
   p.blk_ctr = reinterpret_cast<uint32_t*>(ws + pl.off_ctr);
   p.part = reinterpret_cast<uint32_t*>(ws + pl.off_part);
+  p.trace = skinny_trace_ptr();
+  {
+    const char* e = getenv("QL_CHAIN_DEBUG");
+    p.flags = (e != nullptr && e[0] != 0) ? atoi(e) : 0;
+  }
   const void* kern = pl.fmt == QL_INT8 ? reinterpret_cast<const void*>(decode_chain_kernel<QL_INT8>)
                                        : reinterpret_cast<const void*>(decode_chain_kernel<QL_FP8_E4M3>);
   static SmemAttrOnce once_i8, once_f8;

@@ -531,6 +531,7 @@ skinny_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ 
 
 static long long* g_trace = nullptr;
 void set_skinny_trace(void* buf) { g_trace = static_cast<long long*>(buf); }
+long long* skinny_trace_ptr() { return g_trace; }
 
 static int env_int(const char* name, int dflt) {
   const char* e = getenv(name);

@@ -36,6 +36,7 @@ int launch_skinny_fused(const void* x, int64_t ldx, const void* qw, const float*
 bool skinny_ok(int64_t M, int64_t N, int64_t K, int64_t group);        // pre-quantised path usable
 bool skinny_fused_ok(int64_t M, int64_t N, int64_t K, int64_t group);  // fused path usable (M <= 16)
 bool skinny_fused_preferred(int64_t M, int64_t N, int64_t K, int64_t group);  // ... and the faster choice
+long long* skinny_trace_ptr();
 void set_skinny_trace(void* buf);  // debug: 16 x int64 device buffer, or nullptr
 bool pdl_enabled();  // QL_PDL=0 disables programmatic dependent launch
 
