@@ -444,6 +444,21 @@ bool make_tmap_2d(CUtensorMap* tm, const void* base, CUtensorMapDataType dt, int
   return true;
 }
 
+// The same tensor without swizzle (dense box rows in shared memory, boxes wider than 128 bytes);
+// not cached: the decode chain encodes its maps once, in ql_chain_prepare.
+bool make_tmap_2d_plain(CUtensorMap* tm, const void* base, CUtensorMapDataType dt, int64_t inner, int64_t outer,
+                        int64_t row_stride_bytes, int box_inner, int box_outer) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) return false;
+  cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t gstride[1] = {(cuuint64_t)row_stride_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(tm, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // 2-D uint8 tensor [rows, K] (K contiguous), box = {128 K-bytes, box_rows}
 static bool make_tmap(CUtensorMap* tm, const void* base, int64_t rows, int64_t K, int box_rows) {
   return make_tmap_2d(tm, base, CU_TENSOR_MAP_DATA_TYPE_UINT8, K, rows, K, kBlockK, box_rows);

@@ -119,6 +119,9 @@ int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group);
 bool make_tmap_2d(CUtensorMap* tm, const void* base, CUtensorMapDataType dt, int64_t inner,
                   int64_t outer, int64_t row_stride_bytes, int box_inner, int box_outer);
 
+bool make_tmap_2d_plain(CUtensorMap* tm, const void* base, CUtensorMapDataType dt, int64_t inner,
+                        int64_t outer, int64_t row_stride_bytes, int box_inner, int box_outer);
+
 int num_sms();
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE attribute and the library serves

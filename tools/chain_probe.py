@@ -40,34 +40,26 @@ def timeit(n=20):
     return e0.elapsed_time(e1) / n
 
 
-names = {0: "full", 64: "timer-free waits", 64 + 1: "tf, no mma", 64 + 2: "tf, no barrier wait", 64 + 8: "tf, no weight loads",
-         64 + 16: "tf, no x loads", 64 + 32: "tf, no threadfence", 64 + 9: "tf, no loads, no mma",
-         64 + 63: "tf, everything off"}
-for f, nm in names.items():
-    os.environ["QL_CHAIN_DEBUG"] = str(f)
-    ms = timeit()
-    print(f"flags {f:3d} {nm:28s} {ms * 1e3:9.1f} us/step  {ms * 1e3 / len(ops):7.2f} us/op  {nbytes / ms / 1e6:8.1f} GB/s", flush=True)
+ms = timeit()
+print(f"{model} x{layers} layers M={M}: {ms * 1e3:9.1f} us/step  {ms * 1e3 / len(ops):7.2f} us/op  {nbytes / ms / 1e6:8.1f} GB/s", flush=True)
 
 # clock64 trace of the first 16 ops (per CTA deltas, cycles)
 G = torch.cuda.get_device_properties(0).multi_processor_count
-lab = ["start", "amax sync", "quantised", "1st slot full", "1st slot released", "1st row group", "1st batch mma",
-       "reduce sync", "1st batch stored", "all batches", "fenced", "pre-arrive sync", "arrived", "barrier done"]
-for fl in (0, 64):
-    os.environ["QL_CHAIN_DEBUG"] = str(fl)
-    tr = torch.zeros(G * 16 * 16, dtype=torch.int64, device="cuda")
-    _ext.load().ql_debug_set_trace(tr.data_ptr())
-    chain.run()
-    torch.cuda.synchronize()
-    _ext.load().ql_debug_set_trace(None)
-    t = tr.view(G, 16, 16).cpu().double()
-    print(f"flags {fl}: per-op cycles from op start, median over stamping CTAs (max in brackets)")
-    print("stamps: " + ", ".join(f"{i}={n}" for i, n in enumerate(lab)))
-    for l in range(min(16, len(ops))):
-        row = []
-        for i in range(1, 14):
-            ok = (t[:, l, i] > 0) & (t[:, l, 0] > 0)
-            v = (t[:, l, i] - t[:, l, 0])[ok]
-            row.append("    -    " if v.numel() == 0 else f"{v.median():5.0f}[{v.max():5.0f}]")
-        N, K = ops[l][0].shape
-        print(f"op {l:2d} {N:5d}x{K:5d} " + " ".join(row))
-os.environ["QL_CHAIN_DEBUG"] = "0"
+lab = ["start", "amax sync", "quantised", "1st slot full", "pass-0 mma done", "partials landed", "pass-0 finished",
+       "op finished", "pre-arrive sync", "arrived", "barrier done"]
+tr = torch.zeros(G * 16 * 16, dtype=torch.int64, device="cuda")
+_ext.load().ql_debug_set_trace(tr.data_ptr())
+chain.run()
+torch.cuda.synchronize()
+_ext.load().ql_debug_set_trace(None)
+t = tr.view(G, 16, 16).cpu().double()
+print("per-op cycles from op start, median over stamping CTAs (max in brackets)")
+print("stamps: " + ", ".join(f"{i}={n}" for i, n in enumerate(lab)))
+for l in range(min(16, len(ops))):
+    row = []
+    for i in range(1, 11):
+        ok = (t[:, l, i] > 0) & (t[:, l, 0] > 0)
+        v = (t[:, l, i] - t[:, l, 0])[ok]
+        row.append("    -    " if v.numel() == 0 else f"{v.median():5.0f}[{v.max():5.0f}]")
+    N, K = ops[l][0].shape
+    print(f"op {l:2d} {N:5d}x{K:5d} " + " ".join(row))
