@@ -103,6 +103,30 @@ def main():
         good &= np.array_equal(orc.t2n(q), qo) and float(sc) == sco
         print(f"{'ok  ' if good else 'FAIL'} quantisers fmt={fmt}", flush=True)
         ok &= good
+    # persistent decode chain (clusters, DSMEM reduce-scatter, TMA ring, grid barrier): 4 chained ops,
+    # K splits 4 and 2, an op with its own input, bias
+    g2 = torch.Generator().manual_seed(2)
+    shapes, M = [(264, 384), (128, 256), (1032, 128), (8, 1024)], 5
+    ops, xs = [], []
+    for i, (N, K) in enumerate(shapes):
+        w = (torch.randn(N, K, generator=g2) * 0.05).to(torch.bfloat16)
+        qw, sw = _ext.quant_rows(w.cuda(), torch.int8)
+        b = (torch.randn(N, generator=g2) * 0.1).to(torch.bfloat16).cuda() if i in (0, 2) else None
+        x = torch.randn(M, K, generator=g2).to(torch.bfloat16).cuda() if i in (0, 2) else None
+        ops.append((qw, sw, b, x))
+        xs.append(x)
+    chain = _ext.DecodeChain(ops, M, torch.int8)
+    chain.run()
+    chain.run()
+    torch.cuda.synchronize()
+    good = True
+    for i, (qw, sw, b, _) in enumerate(ops):
+        xin = xs[i] if xs[i] is not None else chain.outputs[i - 1][:, :qw.shape[1]].contiguous()
+        qx, sx = orc.quant_rows(orc.t2n(xin), orc.INT8)
+        yo = orc.gemm_rows(qx, sx, orc.t2n(qw), orc.t2n(sw), None if b is None else orc.t2n(b), orc.INT8)
+        good &= np.array_equal(orc.t2n(chain.outputs[i]), yo)
+    print(f"{'ok  ' if good else 'FAIL'} decode chain", flush=True)
+    ok &= good
     # fused producers
     x, r, wn = rnd((6, 1024), 7), rnd((6, 1024), 8), (1 + 0.1 * torch.randn(1024)).to(torch.bfloat16)
     res = r.cuda()
