@@ -231,7 +231,8 @@ const char* ql_linear_path(int64_t M, int64_t N, int64_t K, int64_t group) {
     return skinny_fused_ok(M, N, K, group) ? "skinny_tcgen05_fused" : "gemv_mma";
   }
   if (skinny_ok(M, N, K, group)) return "skinny_tcgen05";
-  return gemm_kernel_choice(M, N, K, group) == 2 ? "gemm_tcgen05_2cta" : "gemm_tcgen05";
+  const int choice = gemm_kernel_choice(M, N, K, group);
+  return choice == 2 ? "gemm_tcgen05_2cta" : (choice == 3 ? "gemm_tcgen05_2cta_grouped" : "gemm_tcgen05");
 }
 
 int ql_linear(const void* x, int64_t ldx, const void* qw, const float* sw, const void* bias,

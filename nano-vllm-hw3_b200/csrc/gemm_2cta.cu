@@ -456,6 +456,330 @@ gemm2_push_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   gemm2_body<FMT, false, HAS_BIAS, true>(tm_x, tm_w, nullptr, p, &push);
 }
 
+// ------------------------------------------------------------------ per-group scales on the CTA pair
+//
+// per_group_matmul (reference quantization.py:265-307; W8A8 form): weight scales
+// sw[n, j] per `group` values of K.  One TMEM accumulator per 128-byte K block, ping-ponged (2 x 256
+// columns = all of TMEM): while the tensor core fills P_{b+1} the epilogue warps promote P_b into
+// fp32 running sums in REGISTERS, t[n] = fmaf(float(P_b[n]), sw[n, b / blocks_per_group], t[n]), in
+// K order -- the arithmetic of gemm_kernel<GROUPED> and of the oracle's gemm_groups, bit for bit.
+// What bounds it is the TMEM READ path: every K block the whole 128 x 256 x 4 B accumulator of a
+// CTA goes through tcgen05.ld (64 B/clk/SM nominal) -- 64 tensor FLOP per TMEM byte, a ceiling of
+// ~1.2-1.6 PFLOP/s whatever the tile shape (measured: 89 B/clk here, 71 B/clk in gemm_kernel).
+//
+// The 128 x 256 fp32 running sums of a CTA are half of its register file, so this kernel runs
+// SIXTEEN epilogue warps (4 per TMEM lane quarter, 64 feature columns each: t[64] per thread) next
+// to two control warps (TMA producer; TMEM allocator + MMA issuer).  The scales of 8 groups x 256
+// features are staged in shared memory transposed ([group][feature], double buffered, the next
+// panel in flight as registers while the current one is used), so a thread reads the 4 scales of
+// 4 consecutive columns with one broadcast LDS.128.  INT8 partial sums are converted with the
+// exact magic-number add (|P_b| <= 128 * 127^2 < 2^22) instead of the
+// quarter-rate I2F.  Results leave as 16-byte global stores (a thread owns 128 contiguous bytes of
+// its token's row).
+
+constexpr int kG2gEpiWarps = 16;
+constexpr int kG2gThreads = 64 + 32 * kG2gEpiWarps;             // 576
+constexpr int kG2gStages = 5;
+constexpr int kG2gPanel = 8;                                    // scale groups per staged panel
+constexpr int kG2gSwSmem = 2 * kG2gPanel * kG2TileN * 4;        // [2][8][256] fp32
+constexpr int kG2gBiasSmem = 2 * kG2TileN * 4;                  // [2][256] fp32
+constexpr int kG2gSmem = kG2gStages * kG2Stage + kG2gSwSmem + kG2gBiasSmem + 256 + 1024;
+
+struct Gemm2gParams {
+  const float* sx;       // [M]
+  const float* sw;       // [N, G]
+  const uint16_t* bias;  // bf16 [N] or nullptr
+  uint16_t* y;           // bf16 [M, ldy]
+  int64_t ldy;
+  int M, N, K;
+  int G, kb_per_g;       // scale groups along K; 128-byte K blocks per group
+  int tiles_m, tiles_n, group_m;
+};
+
+__device__ __forceinline__ void tmem_ld_wait_regs16(uint32_t (&r)[16]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) asm volatile("" : "+r"(r[i]));
+}
+__device__ __forceinline__ void stg128(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+template <int FMT, bool HAS_BIAS>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kG2gThreads, 1)
+gemm2g_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+              const Gemm2gParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem0 - smem_u32(smem_raw));
+  const uint32_t sw0 = smem0 + kG2gStages * kG2Stage;     // [2][8][256] fp32
+  const uint32_t bias0 = sw0 + kG2gSwSmem;                // [2][256] fp32
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_gen + kG2gStages * kG2Stage + kG2gSwSmem + kG2gBiasSmem);
+  uint64_t* empty_bar = full_bar + kG2gStages;
+  uint64_t* tfull_bar = empty_bar + kG2gStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();   // 0 = leader (issues the MMAs)
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_x);
+    tma_prefetch_desc(&tm_w);
+    for (int i = 0; i < kG2gStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 2 * kG2gEpiWarps);   // epilogue warps of both CTAs
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc2(tmem_slot, 512);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+
+  const int num_kb = p.K / kG2BlockK;
+  const int total_tiles = p.tiles_m * p.tiles_n;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs): as gemm2_body =====================
+    if (lane == 0) {
+      int pre = 0;
+      {
+        int stage = 0;
+        for (int tile = pair; tile < total_tiles && pre < kG2gStages; tile += num_pairs) {
+          int tm, tn;
+          tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+          const int row_b = tn * kG2TileN + (int)cta * kG2RowsB;
+          for (int kb = 0; kb < num_kb && pre < kG2gStages; ++kb, ++pre, ++stage) {
+            const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[stage]), 0);
+            if (cta == 0) mbar_expect_tx(&full_bar[stage], 2 * kG2Stage);
+            tma_load_2d_pair(smem_gen + stage * kG2Stage + kG2StageA, &tm_w, full_leader, kb * kG2BlockK, row_b);
+          }
+        }
+      }
+      pdl_wait();
+      int stage = 0, it = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        int tm, tn;
+        tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+        const int row_a = tm * 2 * kG2RowsA + (int)cta * kG2RowsA;
+        const int row_b = tn * kG2TileN + (int)cta * kG2RowsB;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[stage]), 0);
+          uint8_t* sa = smem_gen + stage * kG2Stage;
+          if (it >= pre) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (cta == 0) mbar_expect_tx(&full_bar[stage], 2 * kG2Stage);
+            tma_load_2d_pair(sa + kG2StageA, &tm_w, full_leader, kb * kG2BlockK, row_b);
+          }
+          tma_load_2d_pair(sa, &tm_x, full_leader, kb * kG2BlockK, row_a);
+          if (++stage == kG2gStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only): one accumulator per scale group ==========
+    if (cta == 0 && lane == 0) {
+      constexpr uint32_t idesc = make_idesc<FMT>(2 * kG2RowsA, kG2TileN);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * kG2TileN;
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem0 + stage * kG2Stage;
+          const uint64_t a_desc = make_sw128_kmajor_desc(sa);
+          const uint64_t b_desc = make_sw128_kmajor_desc(sa + kG2StageA);
+#pragma unroll
+          for (int k = 0; k < kG2BlockK / 32; ++k) {
+            if constexpr (FMT == QL_INT8)
+              mma2_i8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, k > 0);
+            else
+              mma2_f8(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, k > 0);
+          }
+          tc_commit_pair(&empty_bar[stage]);
+          if (++stage == kG2gStages) { stage = 0; phase ^= 1; }
+          tc_commit_pair(&tfull_bar[acc]);
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue: 16 warps, lane quarter q = warp % 4, column quarter cq ========
+    const int ew = warp - 2;
+    const int q = warp & 3, cq = ew >> 2;
+    const int et = threadIdx.x - 64;                       // 0..511
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(cq * 64);
+    const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty_bar[0]), 0);
+    const int panels = (p.G + kG2gPanel - 1) / kG2gPanel;
+    const int pcol = et >> 1, phf = et & 1;                // panel loader: feature column, which 4 groups
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t pbuf = 0, bbuf = 0;                           // scale panel / bias buffers in use
+    pdl_wait();   // sx and the y buffer belong to the previous kernels
+
+    // scales of panel `pn` of the tile with feature origin `n0`: 4 consecutive groups of one column
+    auto load_panel = [&](int n0, int pn) -> float4 {
+      const int n = n0 + pcol, gi = pn * kG2gPanel + phf * 4;
+      if (n < p.N && gi < p.G) return __ldg(reinterpret_cast<const float4*>(p.sw + (size_t)n * p.G + gi));
+      return make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+    auto store_panel = [&](uint32_t buf, const float4& v) {
+      const uint32_t base = sw0 + buf * (kG2gPanel * kG2TileN * 4) + (uint32_t)(phf * 4 * kG2TileN + pcol) * 4u;
+      sts32f(base, v.x);
+      sts32f(base + kG2TileN * 4, v.y);
+      sts32f(base + 2 * kG2TileN * 4, v.z);
+      sts32f(base + 3 * kG2TileN * 4, v.w);
+    };
+    auto load_bias = [&](int n0) -> float {
+      if constexpr (HAS_BIAS) {
+        const int n = n0 + et;
+        return (et < kG2TileN && n < p.N) ? bf16_lo(p.bias[n]) : 0.0f;
+      } else {
+        return 0.0f;
+      }
+    };
+
+    // first tile's first panel (+ bias)
+    if (pair < total_tiles) {
+      int tm, tn;
+      tile_coords(pair, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+      store_panel(0, load_panel(tn * kG2TileN, 0));
+      if constexpr (HAS_BIAS) { if (et < kG2TileN) sts32f(bias0 + et * 4, load_bias(tn * kG2TileN)); }
+    }
+    named_bar_sync(1, 32 * kG2gEpiWarps);
+
+    for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+      int tm, tn;
+      tile_coords(tile, p.tiles_m, p.tiles_n, p.group_m, tm, tn);
+      const int n0 = tn * kG2TileN;
+      const int m = tm * 2 * kG2RowsA + (int)cta * kG2RowsA + q * 32 + lane;
+      // where the NEXT panel comes from once this tile's panels are used up
+      int n0_next = -1;
+      if (tile + num_pairs < total_tiles) {
+        int tm2, tn2;
+        tile_coords(tile + num_pairs, p.tiles_m, p.tiles_n, p.group_m, tm2, tn2);
+        n0_next = tn2 * kG2TileN;
+      }
+      const float sxm = m < p.M ? __ldg(p.sx + m) : 0.0f;
+      float t[64];
+#pragma unroll
+      for (int i = 0; i < 64; ++i) t[i] = 0.0f;
+
+      for (int pn = 0; pn < panels; ++pn) {
+        // the panel after this one (of this tile, or panel 0 of the pair's next tile): in flight
+        // as registers while this panel is used
+        const bool last_panel = pn + 1 == panels;
+        const bool have_next = !last_panel || n0_next >= 0;
+        float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+        float nbias = 0.0f;
+        if (have_next) nxt = last_panel ? load_panel(n0_next, 0) : load_panel(n0, pn + 1);
+        if (last_panel && n0_next >= 0) nbias = load_bias(n0_next);
+        const int g_end = min(p.G, (pn + 1) * kG2gPanel);
+        for (int gk = pn * kG2gPanel * p.kb_per_g; gk < g_end * p.kb_per_g; ++gk) {
+          // K block gk of the tile belongs to scale group gk / kb_per_g; every 128-byte block is
+          // promoted on its own (the engine's per-group semantics: oracle gemm_groups, gp = 128)
+          const int g = gk / p.kb_per_g;
+          const uint32_t srow = sw0 + pbuf * (kG2gPanel * kG2TileN * 4) +
+                                (uint32_t)((g - pn * kG2gPanel) * kG2TileN + cq * 64) * 4u;
+          mbar_wait(&tfull_bar[acc], acc_phase);
+          tc_fence_after();
+          uint32_t r[2][16];
+          const uint32_t tadr = lane_addr + acc * kG2TileN;
+          tmem_ld16(tadr, r[0]);
+          tmem_ld_wait_regs16(r[0]);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            if (c + 1 < 4) tmem_ld16(tadr + (c + 1) * 16, r[(c + 1) & 1]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float4 s4 = lds128f(srow + (uint32_t)(c * 16 + j * 4) * 4u);
+              const float sv[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const uint32_t raw = r[c & 1][j * 4 + e];
+                float a;
+                if constexpr (FMT == QL_INT8) {
+                  // float(P) without the quarter-rate I2F: |P| <= 128 * 127^2 < 2^22, so the integer
+                  // add into the mantissa of 1.5 * 2^23 and the subtraction are both exact
+                  a = __fsub_rn(__uint_as_float(raw + 0x4B400000u), 12582912.0f);
+                } else {
+                  a = __uint_as_float(raw);
+                }
+                t[c * 16 + j * 4 + e] = fmaf(a, sv[e], t[c * 16 + j * 4 + e]);
+              }
+            }
+            if (c + 1 < 4) tmem_ld_wait_regs16(r[(c + 1) & 1]);
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(tempty_leader0 + acc * 8);
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (have_next) {
+          store_panel(pbuf ^ 1, nxt);
+          if constexpr (HAS_BIAS) {
+            if (last_panel && et < kG2TileN) sts32f(bias0 + (bbuf ^ 1) * (kG2TileN * 4) + et * 4, nbias);
+          }
+        }
+        if (!last_panel) {
+          named_bar_sync(1, 32 * kG2gEpiWarps);   // everyone is done with this panel, the next one is staged
+          pbuf ^= 1;
+        }
+      }
+
+      // ---- the tile is complete: (t * sx[m]) (+ bias[n]) -> bf16 -> 128 contiguous bytes of the token row
+      const uint32_t brow = bias0 + bbuf * (kG2TileN * 4) + (uint32_t)(cq * 64) * 4u;
+      const int nb0 = n0 + cq * 64;
+      uint16_t* yrow = p.y + (int64_t)m * p.ldy + nb0;
+#pragma unroll
+      for (int c8 = 0; c8 < 8; ++c8) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __fmul_rn(t[c8 * 8 + e], sxm);
+        if constexpr (HAS_BIAS) {
+          const float4 b0 = lds128f(brow + (uint32_t)(c8 * 8) * 4u), b1 = lds128f(brow + (uint32_t)(c8 * 8 + 4) * 4u);
+          v[0] = __fadd_rn(v[0], b0.x); v[1] = __fadd_rn(v[1], b0.y); v[2] = __fadd_rn(v[2], b0.z); v[3] = __fadd_rn(v[3], b0.w);
+          v[4] = __fadd_rn(v[4], b1.x); v[5] = __fadd_rn(v[5], b1.y); v[6] = __fadd_rn(v[6], b1.z); v[7] = __fadd_rn(v[7], b1.w);
+        }
+        const int nb = nb0 + c8 * 8;
+        if (m < p.M) {
+          if (nb + 8 <= p.N) {
+            stg128(yrow + c8 * 8, pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                   pack_bf16x2(v[6], v[7]));
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              if (nb + e < p.N) yrow[c8 * 8 + e] = f2bf(v[e]);
+          }
+        }
+      }
+      // the next tile's first panel (and bias) was staged above: publish it
+      named_bar_sync(1, 32 * kG2gEpiWarps);
+      pbuf ^= 1;
+      bbuf ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc2(tmem_base, 512);
+}
+
 // ------------------------------------------------------------------ host side
 
 template <int FMT, bool OUT_ACC, bool HAS_BIAS>
@@ -628,6 +952,86 @@ int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* s
                 : launch_g2<QL_INT8, false, false>(qx, qw, y, ldy, p, st);
   return bias ? launch_g2<QL_FP8_E4M3, false, true>(qx, qw, y, ldy, p, st)
               : launch_g2<QL_FP8_E4M3, false, false>(qx, qw, y, ldy, p, st);
+}
+
+// ---- per-group scales on the CTA pair -------------------------------------------------------
+
+template <int FMT, bool HAS_BIAS>
+static int launch_g2g(const void* qx, const void* qw, Gemm2gParams p, cudaStream_t st) {
+  auto kern = gemm2g_kernel<FMT, HAS_BIAS>;
+  static SmemAttrOnce smem_once;
+  if (int e = ensure_max_smem(reinterpret_cast<const void*>(kern), kG2gSmem, smem_once)) return e;
+  CUtensorMap tm_x, tm_w;
+  if (!make_tmap_2d(&tm_x, qx, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.M, p.K, kG2BlockK, kG2RowsA) ||
+      !make_tmap_2d(&tm_w, qw, CU_TENSOR_MAP_DATA_TYPE_UINT8, p.K, p.N, p.K, kG2BlockK, kG2RowsB))
+    return QL_ERR_CUDA;
+  p.tiles_m = (p.M + 2 * kG2RowsA - 1) / (2 * kG2RowsA);
+  p.tiles_n = (p.N + kG2TileN - 1) / kG2TileN;
+  {
+    const int64_t g = (48ll << 20) / (256ll * p.K);
+    p.group_m = (int)(g < 1 ? 1 : (g > p.tiles_m ? p.tiles_m : g));
+  }
+  const int64_t tiles = (int64_t)p.tiles_m * p.tiles_n;
+  static int pairs_max = 0;
+  if (pairs_max == 0) {
+    cudaLaunchConfig_t qc = {};
+    qc.gridDim = dim3(num_sms() & ~1);
+    qc.blockDim = dim3(kG2gThreads);
+    qc.dynamicSmemBytes = kG2gSmem;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &qc) != cudaSuccess || n < 1) {
+      (void)cudaGetLastError();
+      n = num_sms() / 2;
+    }
+    pairs_max = n;
+  }
+  const int pairs = (int)(tiles < pairs_max ? tiles : pairs_max);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * pairs));
+  cfg.blockDim = dim3(kG2gThreads);
+  cfg.dynamicSmemBytes = kG2gSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  const cudaError_t err = cudaLaunchKernelEx(&cfg, kern, tm_x, tm_w, p);
+  count_launch();
+  if (err != cudaSuccess) {
+    if (getenv("QL_DEBUG") != nullptr)
+      fprintf(stderr, "[qlinear_b200] gemm2g launch failed: %s\n", cudaGetErrorString(err));
+    (void)cudaGetLastError();
+    return QL_ERR_CUDA;
+  }
+  return QL_OK;
+}
+
+// float4 scale-panel loads: 4 groups at a time, 16-byte aligned rows of sw
+bool gemm2_grouped_eligible(const void* y, int64_t ldy, const void* sw, int64_t K, int64_t group) {
+  if (group <= 0 || group % kG2BlockK != 0 || K % group != 0) return false;
+  const int64_t G = K / group;
+  return G % 4 == 0 && (reinterpret_cast<uintptr_t>(sw) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0 &&
+         ldy % 8 == 0;
+}
+
+int launch_gemm2_grouped(const void* qx, const float* sx, const void* qw, const float* sw, const void* bias,
+                         void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int fmt, int64_t group,
+                         cudaStream_t st) {
+  if (M == 0 || N == 0) return QL_OK;
+  Gemm2gParams p;
+  p.sx = sx; p.sw = sw;
+  p.bias = static_cast<const uint16_t*>(bias);
+  p.y = static_cast<uint16_t*>(y);
+  p.ldy = ldy;
+  p.M = (int)M; p.N = (int)N; p.K = (int)K;
+  p.G = (int)(K / group);
+  p.kb_per_g = (int)(group / kG2BlockK);
+  p.tiles_m = p.tiles_n = 0;
+  p.group_m = 1;
+  if (fmt == QL_INT8)
+    return bias ? launch_g2g<QL_INT8, true>(qx, qw, p, st) : launch_g2g<QL_INT8, false>(qx, qw, p, st);
+  return bias ? launch_g2g<QL_FP8_E4M3, true>(qx, qw, p, st) : launch_g2g<QL_FP8_E4M3, false>(qx, qw, p, st);
 }
 
 }  // namespace ql

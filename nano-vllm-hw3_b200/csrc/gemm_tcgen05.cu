@@ -530,7 +530,19 @@ static int launch_bt(const void* qx, const void* qw, const GemmParams& p, cudaSt
 // QL_FORCE_GEMM=1|2 (read once) pins the choice for sweeps and tests.
 int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group) {
   (void)K;
-  if (group > 0) return 1;
+  if (group > 0) {
+    // per-group: the CTA-pair kernel (3) from 256 tokens on; QL_GROUPED_PAIR=0 keeps the single-CTA kernel
+    static int pair_ok = -1;
+    if (pair_ok < 0) {
+      const char* e = getenv("QL_GROUPED_PAIR");
+      pair_ok = (e != nullptr && e[0] == '0') ? 0 : ((e != nullptr && e[0] == '2') ? 2 : 1);   // 2: always
+    }
+    // measured (profiles/r2k_sweep_*): the pair kernel wins once its 256 x 256 tiles fill the 74 pairs
+    // and a tile holds >= 16 K blocks; with K = 1024 (8 blocks) the per-tile costs (panel staging,
+    // direct stores) outweigh its faster promotion
+    const int64_t tiles = ((M + 255) / 256) * ((N + 255) / 256);
+    return (pair_ok && M >= 256 && (pair_ok == 2 || (K >= 2048 && tiles >= 64))) ? 3 : 1;
+  }
   static int forced = -1;
   if (forced < 0) {
     const char* e = getenv("QL_FORCE_GEMM");
@@ -547,8 +559,11 @@ int launch_gemm(const void* qx, const float* sx, const void* qw, const float* sw
                 const void* bias, void* y, int64_t ldy, int32_t* out_acc, int64_t M, int64_t N,
                 int64_t K, int fmt, int64_t group, cudaStream_t st) {
   if (M == 0 || N == 0) return QL_OK;
-  if (gemm_kernel_choice(M, N, K, group) == 2 && gemm2_eligible(y, ldy, sw, bias, out_acc != nullptr))
+  const int choice = gemm_kernel_choice(M, N, K, group);
+  if (choice == 2 && gemm2_eligible(y, ldy, sw, bias, out_acc != nullptr))
     return launch_gemm2(qx, sx, qw, sw, bias, y, ldy, out_acc, M, N, K, fmt, st);
+  if (choice == 3 && out_acc == nullptr && gemm2_grouped_eligible(y, ldy, sw, K, group))
+    return launch_gemm2_grouped(qx, sx, qw, sw, bias, y, ldy, M, N, K, fmt, group, st);
   GemmParams p;
   p.sx = sx; p.sw = sw;
   p.bias = static_cast<const uint16_t*>(bias);

@@ -113,6 +113,11 @@ int launch_tp_reduce(const TpView& tp, int64_t M, int64_t N, int fmt, int pushed
                      cudaStream_t st);
 // Which GEMM kernel launch_gemm picks: 1 = single-CTA weight-stationary, 2 = CTA pair.
 int gemm_kernel_choice(int64_t M, int64_t N, int64_t K, int64_t group);
+// Per-group scales on the CTA pair (gemm2g_kernel): 16 epilogue warps, running sums in registers.
+bool gemm2_grouped_eligible(const void* y, int64_t ldy, const void* sw, int64_t K, int64_t group);
+int launch_gemm2_grouped(const void* qx, const float* sx, const void* qw, const float* sw, const void* bias,
+                         void* y, int64_t ldy, int64_t M, int64_t N, int64_t K, int fmt, int64_t group,
+                         cudaStream_t st);
 
 // 2-D tiled TMA descriptor: tensor [outer, inner] with `row_stride_bytes` between rows, box
 // {box_inner, box_outer} elements, 128-byte swizzle, out-of-bounds reads as zero / writes clipped.

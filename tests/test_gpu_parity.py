@@ -10,6 +10,8 @@ Bars:
   L3 reference thresholds  max|y - x@w.T| / max|x@w.T| < 0.08 (per-row, quantization.py:549-553)
                            and < 0.1 (per-group / per-tensor, :583, :615)
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -17,6 +19,7 @@ import torch
 from oracle import oracle as orc
 
 pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 FP_TOL_ULP = 1.0      # of max|y| (one bf16 ulp at the largest magnitude = 2^-7 relative)
 FP_TOL_L2 = 2e-3
@@ -262,6 +265,61 @@ def test_gemm_groups_prefill_sizes_vs_oracle(ext, dn, M, N, K, g):
         assert np.array_equal(bits(y), yo)
     else:
         assert_close_fp(bits(y), yo)
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("M,N,K,g,bias", [(1030, 3330, 2048, 128, True), (2100, 1800, 2048, 512, False),
+                                          (1100, 3080, 3072, 256, True), (2048, 6144, 4096, 128, False)])
+def test_gemm_groups_pair_kernel_vs_oracle(ext, dn, M, N, K, g, bias):
+    """gemm2g_kernel (CTA pair, 16 epilogue warps, running sums in registers), dispatched from 64 pair
+    tiles and K >= 2048: M and N tails, bias, groups of 128 / 256 / 512 (every 128-byte K block is
+    promoted on its own, as in the oracle), up to 32 scale groups (4 panels).  INT8 bit-exact."""
+    assert ext.linear_path(M, N, K, g) == "gemm_tcgen05_2cta_grouped"
+    x, w = rand_bf16((M, K), M + N + g + 2), rand_bf16((N, K), K + N + g + 2, 0.02)
+    w[5, g:2 * g] *= 40.0
+    b = rand_bf16((N,), 41) if bias else None
+    qx, sx = orc.quant_rows(bits(x), FMT[dn])
+    qw, sw = orc.quant_groups(bits(w), g, FMT[dn])
+    args = (dev(qx, DT[dn]), dev(sx, torch.float32), dev(qw, DT[dn]), dev(sw, torch.float32),
+            None if b is None else b.cuda(), DT[dn], g)
+    y = ext.gemm_w8a8(*args)
+    yo = orc.gemm_groups(qx, sx, qw, sw, None if b is None else bits(b), g, FMT[dn])
+    if dn == "i8":
+        assert np.array_equal(bits(y), yo)
+    else:
+        assert_close_fp(bits(y), yo)
+
+
+def test_gemm_groups_pair_equals_single_cta(ext, monkeypatch):
+    """Same arithmetic in both per-group GEMM kernels: identical bits, FP8 included."""
+    import subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import sys, torch
+        sys.path[:0] = [%r, %r]
+        from nanovllm import _ext
+        g = torch.Generator(device="cuda").manual_seed(5)
+        M, N, K, gs = 520, 1032, 1024, 128
+        x = torch.randn(M, K, generator=g, device="cuda").to(torch.bfloat16)
+        w = (torch.randn(N, K, generator=g, device="cuda") * 0.02).to(torch.bfloat16)
+        for dt in (torch.int8, torch.float8_e4m3fn):
+            qw, sw = _ext.quant_groups(w, gs, dt)
+            y = _ext.linear(x, qw, sw, None, dt, gs)
+            torch.save(y.cpu(), sys.argv[1] + str(dt) + ".pt")
+        print(_ext.linear_path(M, N, K, gs))
+    """) % (ROOT, os.path.join(ROOT, "nano-vllm-hw3_b200"))
+    import tempfile
+    outs = {}
+    with tempfile.TemporaryDirectory() as td:
+        for mode in ("2", "0"):
+            env = dict(os.environ, QL_GROUPED_PAIR=mode)
+            r = subprocess.run([sys.executable, "-c", code, os.path.join(td, mode + "_")], env=env,
+                               capture_output=True, text=True, timeout=300)
+            assert r.returncode == 0, r.stderr[-2000:]
+            assert r.stdout.strip() == ("gemm_tcgen05_2cta_grouped" if mode == "2" else "gemm_tcgen05")
+            outs[mode] = [torch.load(os.path.join(td, mode + "_" + str(dt) + ".pt"))
+                          for dt in (torch.int8, torch.float8_e4m3fn)]
+    for a, b in zip(outs["2"], outs["0"]):
+        assert torch.equal(a, b)
 
 
 def test_gemm_rows_fp8_full_size_vs_oracle(ext):
