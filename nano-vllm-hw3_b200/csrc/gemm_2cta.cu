@@ -43,7 +43,12 @@ struct Gemm2Params {
   int M, N, K;
   int tiles_m, tiles_n;  // pair tiles (256 tokens x 256 features)
   int group_m;           // token tiles per rasterisation super-group
+  long long* trace;      // debug (ql_debug_set_trace): globaltimer stamps [launch slot][cta][8], else nullptr
 };
+#define G2_TRACE(i)                                                                                   \
+  do {                                                                                                \
+    if (p.trace != nullptr) p.trace[(size_t)blockIdx.x * 8 + (i)] = (long long)globaltimer_ns();       \
+  } while (0)
 
 // Fused reduce-scatter (PUSH): where the tiles go and whom to tell.
 struct Gemm2Push {
@@ -190,6 +195,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();   // 0 = leader (issues the MMAs)
+  if (threadIdx.x == 0) G2_TRACE(0);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_x);
@@ -215,6 +221,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) G2_TRACE(1);
   pdl_launch_dependents();   // the next kernel (a quantiser) may become resident and wait
 
   const int num_kb = p.K / kG2BlockK;
@@ -244,6 +251,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
         }
       }
       pdl_wait();
+      G2_TRACE(2);
       int stage = 0, it = 0;
       uint32_t phase = 0;
       for (int tile = pair; tile < total_tiles; tile += num_pairs) {
@@ -282,6 +290,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
+          if (tile == pair && kb == 0) G2_TRACE(3);
           const uint32_t sa = smem0 + stage * kG2Stage;
           const uint64_t a_desc = make_sw128_kmajor_desc(sa);
           const uint64_t b_desc = make_sw128_kmajor_desc(sa + kG2StageA);
@@ -299,6 +308,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
         tc_commit_pair(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
+      G2_TRACE(4);
     }
   } else if (warp >= 4) {
     // ===================== epilogue (both CTAs, 8 warps) =====================
@@ -350,6 +360,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
       }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
+      if (threadIdx.x == 128 && tile + num_pairs >= total_tiles) G2_TRACE(5);   // last tile's accumulator is ready
 
       if constexpr (OUT_ACC) {
 #pragma unroll 1
@@ -430,11 +441,13 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
     if (lane == 0) {
       if constexpr (PUSH) tma_store_wait_read<0>(); else tma_store_wait_all();
     }
+    if (threadIdx.x == 128) G2_TRACE(6);
   }
 
   tc_fence_before();
   cluster_sync_all();
   if (warp == 2) tmem_dealloc2(tmem_base, 512);
+  if (threadIdx.x == 0) G2_TRACE(7);
 }
 
 // 128 registers x 384 threads leave a quarter of the register file free: the tensor-parallel
@@ -920,6 +933,7 @@ int launch_gemm2_push(const TpView& tp, const void* qx, const float* sx, const v
   p.sx = sx; p.sw = sw;
   p.bias = static_cast<const uint16_t*>(bias);
   p.acc_out = nullptr;
+  p.trace = nullptr;
   p.M = (int)M; p.N = (int)N; p.K = (int)K;
   p.tiles_m = p.tiles_n = 0;
   p.group_m = 1;
@@ -946,6 +960,12 @@ int launch_gemm2(const void* qx, const float* sx, const void* qw, const float* s
   p.M = (int)M; p.N = (int)N; p.K = (int)K;
   p.tiles_m = p.tiles_n = 0;
   p.group_m = 1;
+  {
+    // debug timeline: launch i of a traced sequence stamps slot i % 8 of the registered buffer
+    static unsigned launch_no = 0;
+    long long* tr = skinny_trace_ptr();
+    p.trace = tr != nullptr ? tr + (size_t)(launch_no++ % 8) * 148 * 8 : nullptr;
+  }
   if (out_acc != nullptr) return launch_g2<QL_INT8, true, false>(qx, qw, y, ldy, p, st);
   if (fmt == QL_INT8)
     return bias ? launch_g2<QL_INT8, false, true>(qx, qw, y, ldy, p, st)
