@@ -252,12 +252,14 @@ class LinearStack:
         return torch.cat(outs)
 
     def micro_batches(self, T):
-        """Two token micro-batches on two streams (one NVLink collective channel each) when the step
-        is tensor-parallel, prefill-sized and the NVLink path with >= 2 channels is up.  Measured
-        (profiles/r2e_*, r2j_*): the split loses 6-9 % at TP = 2 / 4 on Qwen3-0.6B (half-size GEMMs
-        cost more than the overlap wins) and wins 6 % at TP = 8, where the step is bound by the
-        NVLink store rate -- so the default is 2 from 8 ranks up; QL_TP_MICRO=1|2 forces it."""
-        want = os.environ.get("QL_TP_MICRO", "2" if self.tp >= 8 else "1")
+        """QL_TP_MICRO=2: two token micro-batches on two streams (one NVLink collective channel each)
+        when the step is tensor-parallel, prefill-sized and the NVLink path with >= 2 channels is up.
+        Default 1.  Measured (profiles/r2e_*, r2j_*): the split loses 6-9 % at TP = 2 / 4 on
+        Qwen3-0.6B (half-size GEMMs cost more than the overlap wins) and won 6 % in one TP = 8 run
+        -- but a second TP = 8 run of the same configuration ended in the bounded-wait trap (a peer
+        flag never arrived: an ordering hazard between the two channels that the single-channel
+        path does not have), so it stays opt-in."""
+        want = os.environ.get("QL_TP_MICRO", "1")
         if self.tp == 1 or want != "2" or self.layers[0][1].group_size:
             return 1
         from nanovllm import _comm

@@ -49,6 +49,7 @@ struct TpArgs {
   int64_t out_rank_stride;   // emulation: elements between the ranks' `out` tensors
   uint64_t timeout_ns;
   int late_pdl;          // channels run concurrently: release the stream's next kernel only after the cross-GPU waits
+  int ag_pull;           // all-gather of codes + scales by remote LOADS after the done flags (else posted stores)
 };
 
 template <int FMT> struct TpQ { static constexpr float qmax = 1.0f; };
@@ -183,8 +184,12 @@ tp_reduce_kernel(const TpArgs a) {
       uint2 qv[NV];
 #pragma unroll
       for (int i = 0; i < NV; ++i) qv[i] = quant8_mul<FMT>(hv[i], inv);
+      // all-gather: posted stores to every peer as the codes are produced, or (ag_pull) the own copy
+      // only -- the peers fetch it with loads after the done flags
+      const int ndst = a.ag_pull ? 1 : W;
 #pragma unroll
       for (int d = 0; d < W; ++d) {              // own copy first, then the peers, staggered by rank
+        if (d >= ndst) break;
         uint8_t* dbig = a.big[(rank + d) % W];
         uint2* qr = reinterpret_cast<uint2*>(dbig + a.lay.q + (size_t)grow * (size_t)a.N);
 #pragma unroll
@@ -214,6 +219,42 @@ tp_reduce_kernel(const TpArgs a) {
   }
   tp_wait_flags<W>(mine, a.lay.flags + kTpDoneOff, rank, e, a.timeout_ns);
   if (a.late_pdl) pdl_launch_dependents();
+
+  if constexpr (FMT != QL_FMT_BF16) {
+    if (a.ag_pull) {
+      // ---- 3b. fetch the other owners' codes and scales: 8 x 16-byte peer loads in flight per thread.
+      // (An owner rewrites its slice only in its next call, behind that call's ready flags, i.e.
+      //  after every peer has finished this kernel.)
+      constexpr int U = 8;
+      const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+      const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+      for (int d = 1; d < W; ++d) {
+        const int o = (rank + d) % W;
+        const int64_t r0 = (int64_t)o * a.Mo;
+        const int64_t rows_o = a.M - r0 < 0 ? 0 : (a.M - r0 < a.Mo ? a.M - r0 : a.Mo);
+        const int64_t vecs = rows_o * (int64_t)a.N / 16;            // N % 16 == 0 (checked by the host)
+        const uint8_t* src = a.big[o] + a.lay.q + (size_t)r0 * (size_t)a.N;
+        uint8_t* dst = mine + a.lay.q + (size_t)r0 * (size_t)a.N;
+        for (int64_t i = tid; i < vecs; i += nthr * U) {
+          uint4 v[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int64_t j = i + (int64_t)u * nthr;
+            v[u] = j < vecs ? ld_sys128(src + (size_t)j * 16) : make_uint4(0, 0, 0, 0);
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int64_t j = i + (int64_t)u * nthr;
+            if (j < vecs) *reinterpret_cast<uint4*>(dst + (size_t)j * 16) = v[u];
+          }
+        }
+        const float* ssrc = reinterpret_cast<const float*>(a.big[o] + a.lay.s) + r0;
+        float* sdst = reinterpret_cast<float*>(mine + a.lay.s) + r0;
+        for (int64_t i = tid; i < rows_o; i += nthr)
+          sdst[i] = __uint_as_float(ld_acquire_sys(reinterpret_cast<const uint32_t*>(ssrc + i)));
+      }
+    }
+  }
 
   if constexpr (FMT == QL_FMT_BF16) {
     // the peers' rows sit in my gather buffer: copy them next to my own rows in `out`
@@ -332,6 +373,13 @@ int launch_tp_reduce(const TpView& tp, int64_t M, int64_t N, int fmt, int pushed
   a.ldo = ldo;
   a.out_rank_stride = M * ldo;
   a.timeout_ns = tp.timeout_ns;
+  {
+    // QL_TP_AG_PULL=1 (read per launch: tests flip it): all-gather by peer loads.  Off by default:
+    // on 8 x B200 it measured 11.8 ms / step against 10.6 ms with posted stores (profiles/r2n_*);
+    // N % 16 required
+    const char* e = getenv("QL_TP_AG_PULL");
+    a.ag_pull = (N % 16 == 0) && e != nullptr && e[0] == '1';
+  }
   if (fmt == QL_INT8) return launch_tp_fmt<QL_INT8>(a, tp.world, st);
   if (fmt == QL_FP8_E4M3) return launch_tp_fmt<QL_FP8_E4M3>(a, tp.world, st);
   return launch_tp_fmt<QL_FMT_BF16>(a, tp.world, st);

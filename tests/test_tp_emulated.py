@@ -56,6 +56,13 @@ class Emu:
         return torch.cuda.current_stream().cuda_stream
 
 
+@pytest.fixture(params=["ag_push", "ag_pull"])
+def ag_mode(request, monkeypatch):
+    """All-gather of the codes by posted stores or by peer loads after the done flags (QL_TP_AG_PULL)."""
+    monkeypatch.setenv("QL_TP_AG_PULL", "1" if request.param == "ag_pull" else "0")
+    return request.param
+
+
 @pytest.fixture(params=[2, 4, 8])
 def emu(request, ext):
     e = Emu(ext, request.param)
@@ -85,7 +92,7 @@ def _expected(ext, parts, dtype):
 @pytest.mark.parametrize("dn", ["i8", "f8"])
 @pytest.mark.parametrize("M,N", [(512, 1024), (1000, 1024), (300, 2048), (77, 1024), (2304, 4096),
                                  (520, 8192), (4097, 136)])
-def test_pull_reduce_quant_gather(ext, emu, dn, M, N):
+def test_pull_reduce_quant_gather(ext, emu, ag_mode, dn, M, N):
     W, dtype = emu.world, DT[dn]
     parts = _partials(W, M, N, M + N + W)
     for r in range(W):
@@ -121,7 +128,7 @@ def test_pull_allreduce_bf16(ext, emu, M, N):
 @pytest.mark.parametrize("bias", [False, True])
 @pytest.mark.parametrize("M,N,K", [(512, 1024, 256), (1000, 1024, 384), (300, 2048, 128), (2304, 1032, 256),
                                    (4096, 1024, 128)])
-def test_push_gemm_reduce_quant_gather(ext, emu, dn, bias, M, N, K):
+def test_push_gemm_reduce_quant_gather(ext, emu, ag_mode, dn, bias, M, N, K):
     """GEMM + reduce-scatter in one kernel (gemm2_push_kernel): every rank's row-parallel GEMM
     stores its 256-token tiles straight into the owners' receive regions; then the owners reduce."""
     W, dtype = emu.world, DT[dn]
