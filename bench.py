@@ -416,6 +416,43 @@ def decode_leg(stack, m, T, dtype, group, world, peaks, args, dist_on):
     return out
 
 
+def fp8_group_leg(m, T, peaks, args):
+    """BASELINE.json configs[2] / config 3 of SURVEY 8d: FP8-e4m3 weights with one scale per 128
+    values of K (reference per_group_quant / per_group_matmul, quantization.py:194-234, 265-307), the
+    same stack and token count, single GPU: prefill pass and a 16-token decode pass, CUDA-graph
+    replay.  Per-group is bounded by the TMEM READ path, not the tensor pipe (every 128-byte K block
+    the whole accumulator goes through tcgen05.ld to be promoted with its scale: 64 tensor FLOP per
+    TMEM byte), so its fraction of the tensor roofline is expected well below the per-row one."""
+    from nanovllm import _ext
+    stack = LinearStack(m, torch.float8_e4m3fn, "per_group", 128, "cuda", seed=3)
+    out = {"quant": "fp8_e4m3 per_group g=128"}
+    gx = torch.Generator(device="cuda").manual_seed(4)
+    for name, tok in (("prefill", T), ("decode", 16)):
+        x = torch.randn(tok, m["hidden"], generator=gx, device="cuda", dtype=torch.float32).to(torch.bfloat16)
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            stack.forward(x)
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=s):
+                stack.forward(x)
+        torch.cuda.current_stream().wait_stream(s)
+        ms = time_steps(gr.replay, max(args.steps // 2, 5), 3, False)
+        fl, by = flops_bytes(tok, layer_shapes(m), 128)
+        fl, by = fl * m["layers"], by * m["layers"]
+        rec = {"tokens_per_step": tok, "ms_per_step": ms, "value": tok / (ms * 1e-3), "unit": "tokens/s",
+               "path": _ext.linear_path(tok, *layer_shapes(m)[0][1:], 128)}
+        if tok > 16:
+            rec.update(tflops=fl / (ms * 1e-3) / 1e12, frac_of_tensor_peak=fl / (ms * 1e-3) / 1e12 / (2.0 * peaks["bf16"]),
+                       bound="tmem read (tcgen05.ld of every K block's accumulator)")
+        else:
+            rec.update(achieved_gbs=by / (ms * 1e-3) / 1e9, frac_of_hbm_peak=by / (ms * 1e-3) / 1e9 / peaks["hbm"])
+        out[name] = rec
+    del stack
+    torch.cuda.empty_cache()
+    return out
+
+
 # ------------------------------------------------------------------ CPU arm
 
 def cpu_model_name():
@@ -532,6 +569,7 @@ def main():
     ap.add_argument("--quant", default="per_row", choices=["per_row", "per_group"])
     ap.add_argument("--group-size", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-legs", action="store_true", help="skip the FP8 g=128 leg")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
     ap.add_argument("--kernel-table", default=None, metavar="PATH",
                     help="AFTER the line is printed: replay 3 steps under the CUPTI kernel tracer and write "
@@ -704,6 +742,11 @@ def main():
     if T_rank > 16:
         decode = decode_leg(stack, m, 16 * world, dtype, group, world, peaks, args, dist_on)
 
+    # ---- FP8 g=128 leg (the reference's per-group configuration), default workload only
+    fp8_g128 = None
+    if world == 1 and group == 0 and T_rank > 16 and args.model == "0.6b" and not args.no_extra_legs:
+        fp8_g128 = fp8_group_leg(m, T, peaks, args)
+
     # ---- dominant kernel alone (roofline): the GEMM (or GEMV for T <= 16) over all local weights
     shapes = layer_shapes(m, world)
     fl_layer, by_layer = flops_bytes(T, shapes, group)
@@ -772,6 +815,8 @@ def main():
     }
     if decode is not None:
         line["decode"] = decode
+    if fp8_g128 is not None:
+        line["fp8_g128"] = fp8_g128
     if tp_info is not None:
         line["tp_check"] = tp_info["status"]
         line["tp_collective"] = tp_info

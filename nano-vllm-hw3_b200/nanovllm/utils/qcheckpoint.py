@@ -72,6 +72,22 @@ def load_quantized(named_layers: dict, path: str, device="cuda") -> None:
             dtype, g = _DT[dt_name], int(g)
             qw, sw = f.get_tensor(f"{name}.qweight"), f.get_tensor(f"{name}.scale")
             bias = f.get_tensor(f"{name}.bias") if f"{name}.bias" in f.keys() else None
+            # the file must describe THIS layer (full, TP=1 shapes): a mismatched or partial file
+            # must not load silently
+            tp = layer.tp_size
+            ref = layer.weight if getattr(layer, "weight", None) is not None else layer.qw
+            n_full = ref.shape[0] * (tp if layer.tp_dim == 0 else 1)
+            k_full = ref.shape[1] * (tp if layer.tp_dim == 1 else 1)
+            if tuple(qw.shape) != (n_full, k_full):
+                raise ValueError(f"{name}: qweight {tuple(qw.shape)} does not match the layer ({n_full}, {k_full})")
+            n_sw = n_full * (k_full // g) if quant_type == "per_group" else n_full
+            if sw.dtype != torch.float32 or sw.numel() != n_sw or sw.shape[0] != n_full:
+                raise ValueError(f"{name}: scale {tuple(sw.shape)} / {sw.dtype} does not match "
+                                 f"{n_sw} fp32 values in {n_full} rows")
+            if layer.bias is not None and bias is None:
+                raise ValueError(f"{name}: the layer has a bias but the checkpoint has none")
+            if bias is not None and bias.numel() != n_full:
+                raise ValueError(f"{name}: bias has {bias.numel()} entries, the layer {n_full}")
             if layer.tp_size > 1 and layer.tp_dim == 0:
                 rows = torch.cat([torch.arange(a, a + n) for a, n in _sub_ranges(layer, qw.shape[0])])
                 qw, sw = qw[rows], sw[rows]

@@ -167,3 +167,34 @@ def test_checkpoint_roundtrip_forward_identical(tmp_path, quant_type):
         xin = x if "gate_up" in name else torch.randn(40, 3072, device="cuda").to(torch.bfloat16)
         assert dst[name].weight is None
         assert torch.equal(src[name](xin), dst[name](xin)), name
+
+
+def test_checkpoint_rejects_mismatched_file(tmp_path, monkeypatch):
+    """A checkpoint written for other shapes, or one without the bias a layer has, must not load."""
+    import pytest
+    from nanovllm.layers.linear import ReplicatedLinear
+    from nanovllm.utils import qcheckpoint
+    from safetensors.torch import save_file
+    import json
+    N, K = 16, 128
+    good = {"l.qweight": torch.zeros(N, K, dtype=torch.int8).view(torch.uint8), "l.scale": torch.ones(N)}
+    meta = {"qlinear_b200": json.dumps({"l": "int8,per_row,0"})}
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    try:
+        layer = ReplicatedLinear(K, N, bias=True)
+        other = ReplicatedLinear(K, 2 * N)
+    finally:
+        torch.set_default_dtype(prev)
+    p = str(tmp_path / "q.safetensors")
+    save_file(good, p, metadata=meta)
+    with pytest.raises(ValueError, match="bias"):
+        qcheckpoint.load_quantized({"l": layer}, p, device="cpu")
+    with pytest.raises(ValueError, match="qweight"):
+        qcheckpoint.load_quantized({"l": other}, p, device="cpu")
+    bad = dict(good)
+    bad["l.scale"] = torch.ones(N + 1)
+    save_file(bad, p, metadata=meta)
+    layer2 = ReplicatedLinear(K, N)
+    with pytest.raises(ValueError, match="scale"):
+        qcheckpoint.load_quantized({"l": layer2}, p, device="cpu")
