@@ -303,13 +303,19 @@ QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);
  * Every op is y = bf16((acc * sx[m]) * sw[n] + bias[n]) on per-token-quantised x, per-row weight
  * scales, exactly as ql_linear (INT8: bit-identical; FP8: fp32 summation order differs).
  *   ql_chain_workspace_bytes: device scratch the chain needs (0 = the chain is not supported:
- *     M > 16, K % 128, N % 8, a slice plan that does not fit ...);
- *   ql_chain_prepare: plans the chain for the current device, writes the device-side descriptors
- *     into `workspace` (256-byte aligned, stays owned by the caller, must outlive every run) and
- *     fills `plan`; synchronises `stream`; NOT capturable.  The op array, M, every pointer and
- *     pitch are frozen into the workspace: prepare again when any of them changes;
- *   ql_chain_run: ONE kernel launch (cooperative: one CTA per SM, all co-resident); capturable
- *     into a CUDA graph.  Runs of one workspace must not overlap each other.
+ *     M > 16, K % 128, N % 8, K > 12288 ...);
+ *   ql_chain_prepare: plans the chain for the current device (clusters of 4 CTAs, as many as
+ *     cudaOccupancyMaxActiveClusters reports co-resident), encodes one TMA descriptor per op,
+ *     writes descriptors and plan tables into `workspace` (256-byte aligned, stays owned by the
+ *     caller, must outlive every run) and fills `plan`; synchronises `stream`; NOT capturable.
+ *     The op array, M, every pointer and pitch are frozen into the workspace: prepare again when
+ *     any of them changes;
+ *   ql_chain_run: ONE kernel launch (cooperative + cluster launch, one CTA per SM, all
+ *     co-resident; every CTA spins on a bounded grid barrier between ops); capturable into a CUDA
+ *     graph.  Runs of one workspace must not overlap each other.
+ * Measured on B200: correct but SLOWER than one ql_linear per op (a
+ * dependent op costs ~5 us of release / barrier / activation round trips either way); kept as an
+ * experiment that bench.py reports next to the per-linear launches.
  * group must be 0 (per-group scales: use ql_linear).
  */
 typedef struct ql_chain_op {
