@@ -486,8 +486,7 @@ gemm2_push_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 // features are staged in shared memory transposed ([group][feature], double buffered, the next
 // panel in flight as registers while the current one is used), so a thread reads the 4 scales of
 // 4 consecutive columns with one broadcast LDS.128.  INT8 partial sums are converted with the
-// exact magic-number add (|P_b| <= 128 * 127^2 < 2^22) instead of the
-// quarter-rate I2F.  Results leave as 16-byte global stores (a thread owns 128 contiguous bytes of
+// exact magic-number add (|P_b| <= 128 * 127^2 < 2^22: IADD + FADD).  Results leave as 16-byte global stores (a thread owns 128 contiguous bytes of
 // its token's row).
 
 constexpr int kG2gEpiWarps = 16;
@@ -727,7 +726,7 @@ gemm2g_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ 
                 const uint32_t raw = r[c & 1][j * 4 + e];
                 float a;
                 if constexpr (FMT == QL_INT8) {
-                  // float(P) without the quarter-rate I2F: |P| <= 128 * 127^2 < 2^22, so the integer
+                  // float(P) by integer add + FADD: |P| <= 128 * 127^2 < 2^22, so the integer
                   // add into the mantissa of 1.5 * 2^23 and the subtraction are both exact
                   a = __fsub_rn(__uint_as_float(raw + 0x4B400000u), 12582912.0f);
                 } else {
