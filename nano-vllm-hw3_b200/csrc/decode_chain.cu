@@ -17,11 +17,12 @@
 //   * thread-block CLUSTERS of 4 CTAs split K: rank r of a cluster reads and quantises only ITS
 //     K/4 slice of the activation (Triton quantiser arithmetic :26-41, bit for bit) and streams
 //     only that slice of its weight rows; the four partial accumulator tiles meet through
-//     DISTRIBUTED SHARED MEMORY (reduce-scatter: 8-row group i goes to rank i % 4, summed in rank
-//     order -- int32: exact, fp32: fixed order), no L2 round trip, no second grid barrier;
+//     DISTRIBUTED SHARED MEMORY (reduce-scatter: 8-row group i goes to rank i % 4 by st.async, the
+//     bytes counted on the receiver's mbarrier -- no fences; summed in rank order -- int32: exact,
+//     fp32: fixed order), no L2 round trip, no second grid barrier;
 //   * rows are dealt to the clusters in groups of 8 (the mma.sync n = 8), so every SM gets the
 //     same bytes +- one group for any N; weights arrive by TMA (one 8-row x <= 512-byte box per
-//     instruction) through a 34-slot ring that runs ahead ACROSS op boundaries (weights depend on
+//     instruction, two TMA warps) through a 34-slot ring that runs ahead ACROSS op boundaries (weights depend on
 //     nothing): HBM keeps streaming while an op's epilogue and the grid barrier are in flight;
 //   * each consumer warp owns whole row groups (its own ring slots, its own accumulators in
 //     registers: m16n8k32 warp MMAs, int8 -> int32 exact / e4m3 -> fp32), activations as
@@ -30,10 +31,19 @@
 //     :111-121 --, stores bf16 and folds |y| into the NEXT op's per-token amax (atomicMax on the
 //     float bit pattern), so the next op's quantiser needs no pass over the row;
 //   * ONE grid barrier per op (red.release.gpu by one thread per CTA + ld.acquire.gpu spin);
-//     static data (descriptors, first scales) is fetched one op ahead.
+//     static data is fetched ahead of its use: op descriptors two ops ahead into shared memory,
+//     the TMA warps read the next op's plan and prefetch its tensor map while issuing this op's
+//     boxes, the scales / bias of a pass are loaded before its weight stream and staged in shared
+//     memory.
 //
 // Results are bit-identical to ql_linear op by op for INT8 per-row (int32 accumulation is exact in
 // any order); FP8 per-row differs from the tcgen05 kernels only in fp32 summation order.
+//
+// OUTCOME: correct, and slower than one ql_linear per op on every Qwen3
+// stack measured (0.6B 7.2 vs 5.4 us per op, 8B 19.5 vs 12 us): the dependent chain release ->
+// grid barrier -> activation read -> quantise -> first MMAs -> exchange -> epilogue costs ~10 000
+// cycles per op, more than a kernel boundary with programmatic dependent launch.  bench.py times
+// it next to the per-linear launches; nothing else in the engine depends on it.
 #include <cuda.h>
 #include <stdio.h>
 #include <stdlib.h>
