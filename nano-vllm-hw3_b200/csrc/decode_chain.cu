@@ -21,8 +21,9 @@
 //     bytes counted on the receiver's mbarrier -- no fences; summed in rank order -- int32: exact,
 //     fp32: fixed order), no L2 round trip, no second grid barrier;
 //   * rows are dealt to the clusters in groups of 8 (the mma.sync n = 8), so every SM gets the
-//     same bytes +- one group for any N; weights arrive by TMA (one 8-row x <= 512-byte box per
-//     instruction, two TMA warps) through a 34-slot ring that runs ahead ACROSS op boundaries (weights depend on
+//     same bytes +- one group for any N; weights arrive by TMA (one 8-row x <= 1 KB box per
+//     instruction -- whole DRAM pages per row: with 512-byte rows the stream reached 5 TB/s, with
+//     1 KB rows the HBM peak --, two TMA warps) through a 17-slot ring that runs ahead ACROSS op boundaries (weights depend on
 //     nothing): HBM keeps streaming while an op's epilogue and the grid barrier are in flight;
 //   * each consumer warp owns whole row groups (its own ring slots, its own accumulators in
 //     registers: m16n8k32 warp MMAs, int8 -> int32 exact / e4m3 -> fp32), activations as
@@ -40,7 +41,7 @@
 // any order); FP8 per-row differs from the tcgen05 kernels only in fp32 summation order.
 //
 // OUTCOME: correct, and slower than one ql_linear per op on every Qwen3
-// stack measured (0.6B 7.2 vs 5.4 us per op, 8B 19.5 vs 12 us): the dependent chain release ->
+// stack measured (0.6B 7.2 vs 5.4 us per op, 8B 15.9 vs 12 us): the dependent chain release ->
 // grid barrier -> activation read -> quantise -> first MMAs -> exchange -> epilogue costs ~10 000
 // cycles per op, more than a kernel boundary with programmatic dependent launch.  bench.py times
 // it next to the per-linear launches; nothing else in the engine depends on it.
@@ -61,9 +62,10 @@ constexpr int kDcThreads = kDcConsumers + 32 * kDcProducers;
 constexpr int kDcJ = 8;                        // row groups per warp per pass
 constexpr int kDcPassRG = 8 * kDcJ;            // row groups per CTA per pass
 constexpr int kDcMaxBlk = 48;                  // 64-byte K blocks per rank slice (3072 B: K <= 12288)
-constexpr int kDcChunkBlk = 8;                 // 64-byte K blocks per chunk (<= 512 B of K per slot row)
-constexpr int kDcSlotBytes = 8 * kDcChunkBlk * 64;   // 4 KB: 8 weight rows x <= 512 B
-constexpr int kDcSlots = 34;
+constexpr int kDcChunkBlk = 8;                 // 64-byte K blocks whose A fragments a warp holds at a time
+constexpr int kDcSlotBlk = 16;                 // 64-byte K blocks per ring slot row (<= 1 KB: whole DRAM pages per row)
+constexpr int kDcSlotBytes = 8 * kDcSlotBlk * 64;    // 8 KB: 8 weight rows x <= 1 KB
+constexpr int kDcSlots = 17;
 constexpr int kDcABytes = kDcMaxBlk * 1024;    // quantised activation slice in mma-fragment order
 constexpr int kDcRecvBytes = kDcPassRG * 512;  // partial tiles received from the cluster
 constexpr int kDcSmall = 2048 + 2 * kDcPassRG * 8 * 4;   // barriers, descriptors + staged scales / bias of a pass
@@ -231,14 +233,21 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
         }
         for (int r0p = u.rg0; r0p < u.rg1; r0p += kDcPassRG) {
           const int n = u.rg1 - r0p < kDcPassRG ? u.rg1 - r0p : kDcPassRG;
-          for (int c = 0; c < nch; ++c) {
-            const int c0 = (ksl_blk + c * cbc) * 16;   // uint32 elements along K
-            for (int i = 0; i < n; ++i, ++seq) {
-              if ((seq & 1u) != pw) continue;
-              const uint32_t slot = seq % kDcSlots, par = (seq / kDcSlots) & 1u;
-              mbar_wait(&empty_bar[slot], par ^ 1u);
-              mbar_expect_tx(&full_bar[slot], bytes);
-              tma_load_2d(ring + slot * kDcSlotBytes, tm, &full_bar[slot], c0, (r0p + i) * 8, kEvictFirst);
+          // Blocks of 8 row groups (one per consumer warp), chunk-major inside a block: the chunks of
+          // a row group follow each other within 8 slots (32 KB), so its row segments are fetched
+          // close together (DRAM page reuse), and a warp's consecutive slots are 8 apart -- never
+          // more than one ring lap ahead of the producer (mbarrier parity waits tolerate only one).
+          for (int i0 = 0; i0 < n; i0 += 8) {
+            const int m = n - i0 < 8 ? n - i0 : 8;
+            for (int c = 0; c < nch; ++c) {
+              const int c0 = (ksl_blk + c * cbc) * 16;   // uint32 elements along K
+              for (int w = 0; w < m; ++w, ++seq) {
+                if ((seq & 1u) != pw) continue;
+                const uint32_t slot = seq % kDcSlots, par = (seq / kDcSlots) & 1u;
+                mbar_wait(&empty_bar[slot], par ^ 1u);
+                mbar_expect_tx(&full_bar[slot], bytes);
+                tma_load_2d(ring + slot * kDcSlotBytes, tm, &full_bar[slot], c0, (r0p + i0 + w) * 8, kEvictFirst);
+              }
             }
           }
         }
@@ -248,7 +257,6 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
   } else {
     // ===================== consumers =====================
     const int g = lane >> 2, t = lane & 3;                 // mma fragment coordinates
-    const int e_m = (tid & 127) >> 3, e_j = tid & 7, e_h = tid >> 7;   // finalizer: token, row in group, tile parity
     uint32_t seq_base = 0;                                  // ring sequence number of this pass's first slot
     uint32_t n_exch = 0;                                    // DSMEM exchanges this cluster has done
     const uint32_t recv_local = smem_u32(recv), recv_bar_local = smem_u32(recv_bar),
@@ -325,10 +333,10 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
           if (base + 4 * kDcConsumers < nitems) load_items(base + 4 * kDcConsumers);
         }
         consumer_sync();
+        if (tid < 16) amax_s[tid] = 0;        // from here on: running max of |y| for the NEXT op (finalize)
         DC_TRACE(2);
 
         // ---- passes of <= 64 row groups: stream, exchange, finish -------------------------------
-        float run_max = 0.0f;
         int pass = 0;
         for (int r0c = 0; r0c < u.nrg_max; r0c += kDcPassRG, ++pass) {
           const int r0p = u.rg0 + r0c;
@@ -351,33 +359,40 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
           acc_t acc[kDcJ][4];
 #pragma unroll
           for (int j = 0; j < kDcJ; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0;
-          for (int c = 0; c < nchunk; ++c) {
-            uint4 a_lo[kDcChunkBlk], a_hi[kDcChunkBlk];
 #pragma unroll
-            for (int b = 0; b < kDcChunkBlk; ++b) {
-              if (b < cb) {
-                a_lo[b] = A_s[((c * cb + b) * 2 + 0) * 32 + lane];
-                a_hi[b] = A_s[((c * cb + b) * 2 + 1) * 32 + lane];
-              }
-            }
-#pragma unroll
-            for (int j = 0; j < kDcJ; ++j) {
-              if (j < nj) {
-                const uint32_t s = seq_base + (uint32_t)(c * n + warp + 8 * j);
+          for (int j = 0; j < kDcJ; ++j) {
+            if (j < nj) {
+              for (int c = 0; c < nchunk; ++c) {
+                const int mj = n - 8 * j < 8 ? n - 8 * j : 8;      // row groups in this block of 8
+                const uint32_t s = seq_base + (uint32_t)(8 * j * nchunk + c * mj + warp);
                 const uint32_t slot = s % kDcSlots, par = (s / kDcSlots) & 1u;
-                mbar_wait(&full_bar[slot], par);
-                if (j == 0 && c == 0 && pass == 0) DC_TRACE(3);
                 const uint8_t* wrow = ring + slot * kDcSlotBytes + g * (cb * 64) + t * 16;
+                // a slot row holds cb <= 16 blocks; the warp keeps the A fragments of 8 at a time
+                for (int h0 = 0; h0 < cb; h0 += kDcChunkBlk) {
+                  const int hb = cb - h0 < kDcChunkBlk ? cb - h0 : kDcChunkBlk;
+                  uint4 a_lo[kDcChunkBlk], a_hi[kDcChunkBlk];
 #pragma unroll
-                for (int b = 0; b < kDcChunkBlk; ++b) {
-                  if (b < cb) {
-                    const uint4 w = *reinterpret_cast<const uint4*>(wrow + b * 64);
-                    if constexpr (FMT == QL_INT8) {
-                      mma_i8_sync(acc[j], a_lo[b].x, a_hi[b].x, a_lo[b].y, a_hi[b].y, w.x, w.y);
-                      mma_i8_sync(acc[j], a_lo[b].z, a_hi[b].z, a_lo[b].w, a_hi[b].w, w.z, w.w);
-                    } else {
-                      mma_f8_sync(acc[j], a_lo[b].x, a_hi[b].x, a_lo[b].y, a_hi[b].y, w.x, w.y);
-                      mma_f8_sync(acc[j], a_lo[b].z, a_hi[b].z, a_lo[b].w, a_hi[b].w, w.z, w.w);
+                  for (int b = 0; b < kDcChunkBlk; ++b) {
+                    if (b < hb) {
+                      a_lo[b] = A_s[((c * cb + h0 + b) * 2 + 0) * 32 + lane];
+                      a_hi[b] = A_s[((c * cb + h0 + b) * 2 + 1) * 32 + lane];
+                    }
+                  }
+                  if (h0 == 0) {
+                    mbar_wait(&full_bar[slot], par);
+                    if (j == 0 && c == 0 && pass == 0) DC_TRACE(3);
+                  }
+#pragma unroll
+                  for (int b = 0; b < kDcChunkBlk; ++b) {
+                    if (b < hb) {
+                      const uint4 w = *reinterpret_cast<const uint4*>(wrow + (h0 + b) * 64);
+                      if constexpr (FMT == QL_INT8) {
+                        mma_i8_sync(acc[j], a_lo[b].x, a_hi[b].x, a_lo[b].y, a_hi[b].y, w.x, w.y);
+                        mma_i8_sync(acc[j], a_lo[b].z, a_hi[b].z, a_lo[b].w, a_hi[b].w, w.z, w.w);
+                      } else {
+                        mma_f8_sync(acc[j], a_lo[b].x, a_hi[b].x, a_lo[b].y, a_hi[b].y, w.x, w.y);
+                        mma_f8_sync(acc[j], a_lo[b].z, a_hi[b].z, a_lo[b].w, a_hi[b].w, w.z, w.w);
+                      }
                     }
                   }
                 }
@@ -420,25 +435,56 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
           mbar_wait(recv_bar, n_exch & 1u);
           if (pass == 0) DC_TRACE(5);
 
-          // ---- finish the tiles this rank owns: idx = ts * kse + ksl -----------------------------
-          for (int ts = e_h; ts * kse + u.ksl < n; ts += 2) {
+          // ---- finish the tiles this rank owns (idx = ts * kse + ksl): one (tile, token) per thread =
+          // 8 consecutive features: 2 x LDS.128 per source rank, one 16-byte store
+          for (int it = tid; it < my_tiles * 16; it += kDcConsumers) {
+            const int ts = it >> 4, m = it & 15;
             const int idx = ts * kse + u.ksl;
-            const uint32_t* rs = recv + ts * 128 + (tid & 127);
-            uint32_t sum = rs[0];
+            const uint4* rs = reinterpret_cast<const uint4*>(recv + ts * 128 + m * 8);
+            uint4 s0 = rs[0], s1 = rs[1];
             for (int s = 1; s < kse; ++s) {
-              const uint32_t o = rs[s * tps * 128];
-              if constexpr (FMT == QL_INT8) sum = (uint32_t)((int)sum + (int)o);
-              else sum = __float_as_uint(__fadd_rn(__uint_as_float(sum), __uint_as_float(o)));
+              const uint4 o0 = rs[s * tps * 32], o1 = rs[s * tps * 32 + 1];
+              if constexpr (FMT == QL_INT8) {
+                s0.x += o0.x; s0.y += o0.y; s0.z += o0.z; s0.w += o0.w;
+                s1.x += o1.x; s1.y += o1.y; s1.z += o1.z; s1.w += o1.w;
+              } else {
+                s0.x = __float_as_uint(__fadd_rn(__uint_as_float(s0.x), __uint_as_float(o0.x)));
+                s0.y = __float_as_uint(__fadd_rn(__uint_as_float(s0.y), __uint_as_float(o0.y)));
+                s0.z = __float_as_uint(__fadd_rn(__uint_as_float(s0.z), __uint_as_float(o0.z)));
+                s0.w = __float_as_uint(__fadd_rn(__uint_as_float(s0.w), __uint_as_float(o0.w)));
+                s1.x = __float_as_uint(__fadd_rn(__uint_as_float(s1.x), __uint_as_float(o1.x)));
+                s1.y = __float_as_uint(__fadd_rn(__uint_as_float(s1.y), __uint_as_float(o1.y)));
+                s1.z = __float_as_uint(__fadd_rn(__uint_as_float(s1.z), __uint_as_float(o1.z)));
+                s1.w = __float_as_uint(__fadd_rn(__uint_as_float(s1.w), __uint_as_float(o1.w)));
+              }
             }
-            if (e_m < p.M) {
-              const int nn = (r0p + idx) * 8 + e_j;
-              const float swv = sw_s[idx * 8 + e_j], bv = b_s[idx * 8 + e_j];
-              const float a = FMT == QL_INT8 ? __int2float_rn((int)sum) : __uint_as_float(sum);
-              float v = __fmul_rn(__fmul_rn(a, sx_s[e_m]), swv);        // (acc * sa) * sb, reference :121
-              if (bias != nullptr) v = __fadd_rn(v, bv);
-              const uint16_t o = f2bf(v);
-              y[(size_t)e_m * ldy + nn] = o;
-              if (nn < amax_cols) run_max = fmaxf(run_max, fabsf(bf16_lo(o)));
+            if (m < p.M) {
+              const uint32_t raw[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+              const float sxm = sx_s[m];
+              const float4 w0 = *reinterpret_cast<const float4*>(sw_s + idx * 8),
+                           w1 = *reinterpret_cast<const float4*>(sw_s + idx * 8 + 4);
+              const float4 c0 = *reinterpret_cast<const float4*>(b_s + idx * 8),
+                           c1 = *reinterpret_cast<const float4*>(b_s + idx * 8 + 4);
+              const float swv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+              const float bv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+              const int nn = (r0p + idx) * 8;
+              uint16_t o16[8];
+              float mx = 0.0f;
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const float a = FMT == QL_INT8 ? __int2float_rn((int)raw[e]) : __uint_as_float(raw[e]);
+                float v = __fmul_rn(__fmul_rn(a, sxm), swv[e]);            // (acc * sa) * sb, reference :121
+                if (bias != nullptr) v = __fadd_rn(v, bv[e]);
+                o16[e] = f2bf(v);
+                if (nn + e < amax_cols) mx = fmaxf(mx, fabsf(bf16_lo(o16[e])));
+              }
+              uint4 pk;
+              pk.x = o16[0] | ((uint32_t)o16[1] << 16);
+              pk.y = o16[2] | ((uint32_t)o16[3] << 16);
+              pk.z = o16[4] | ((uint32_t)o16[5] << 16);
+              pk.w = o16[6] | ((uint32_t)o16[7] << 16);
+              *reinterpret_cast<uint4*>(y + (size_t)m * ldy + nn) = pk;
+              if (mx > 0.0f) atomicMax(amax_s + m, __float_as_int(mx));   // shared: this op's input amax is consumed
             }
           }
           consumer_sync();
@@ -447,14 +493,9 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
           if (pass == 0) DC_TRACE(6);
         }
 
-        // ---- fold |y| into the next op's per-token amax ------------------------------------------
-        if (amax_cols > 0) {
-          run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 1));
-          run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 2));
-          run_max = fmaxf(run_max, __shfl_xor_sync(0xffffffffu, run_max, 4));
-          if (e_j == 0 && e_m < p.M && run_max > 0.0f)
-            atomicMax(reinterpret_cast<int*>(p.amax) + (l + 1) * 16 + e_m, __float_as_int(run_max));
-        }
+        // ---- fold |y| into the next op's per-token amax (collected per CTA in amax_s) ---------------
+        if (amax_cols > 0 && tid < 16 && tid < p.M && amax_s[tid] > 0)
+          atomicMax(reinterpret_cast<int*>(p.amax) + (l + 1) * 16 + tid, amax_s[tid]);
         DC_TRACE(7);
       }
 
@@ -573,14 +614,15 @@ static int plan_chain(const ql_chain_op* ops, int n_ops, int64_t M, int clusters
     const int64_t ldx = chained ? ops[l - 1].ldy : o.ldx;
     if (chained && ops[l - 1].N < o.K) return QL_ERR_BAD_SHAPE;
     if (ldx < o.K) return QL_ERR_BAD_SHAPE;
-    if ((reinterpret_cast<uintptr_t>(x) & 15) || ldx % 8 != 0 || (reinterpret_cast<uintptr_t>(o.qw) & 15))
+    if ((reinterpret_cast<uintptr_t>(x) & 15) || ldx % 8 != 0 || (reinterpret_cast<uintptr_t>(o.qw) & 15) ||
+        (reinterpret_cast<uintptr_t>(o.y) & 15) || o.ldy % 8 != 0)
       return QL_ERR_MISALIGNED;
     const int nb64 = (int)(o.K / 64);
     const int kse = nb64 % 4 == 0 ? 4 : 2;                // K % 128 == 0: at least 2 blocks
     const int nblk = nb64 / kse;
     if (nblk > kDcMaxBlk) return QL_ERR_BAD_SHAPE;
     int cb = 1;
-    for (int d = kDcChunkBlk; d >= 1; --d)
+    for (int d = kDcSlotBlk; d >= 1; --d)
       if (nblk % d == 0) { cb = d; break; }
     if (dev_ops != nullptr) {
       ChainOp& d = dev_ops[l];
