@@ -416,6 +416,73 @@ def decode_leg(stack, m, T, dtype, group, world, peaks, args, dist_on):
     return out
 
 
+def model_shaped_leg(stack, m, T, dtype, args):
+    """The decoder layer's data flow around the same 112 quantized linears, with the producers the
+    model really has (reference models/qwen3.py:147-167, 114-119): add + RMSNorm -> qkv -> [attention
+    stand-in: the leading k_o columns] -> o -> add + RMSNorm -> gate_up -> SiLU * mul -> down.
+    `fused` = the producers hand the linears their input already quantised (ql_rmsnorm_quant,
+    ql_silu_mul_quant: SURVEY 8f-1; 5 launches fewer per layer); `unfused` = reference structure
+    (bf16 norm / activation, then the linear's own per_row_quant).  Same bits either way."""
+    from nanovllm import _ext
+    from nanovllm.layers.activation import SiluAndMul
+    from nanovllm.layers.layernorm import RMSNorm
+    prev = torch.get_default_dtype()
+    torch.set_default_dtype(torch.bfloat16)
+    with torch.device("cuda"):
+        norms = [(RMSNorm(m["hidden"]), RMSNorm(m["hidden"])) for _ in stack.layers]
+    torch.set_default_dtype(prev)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    for a, b in norms:
+        for n in (a, b):
+            n.weight.data.copy_(1.0 + 0.1 * torch.randn(m["hidden"], generator=g, device="cuda"))
+    act = SiluAndMul()
+    k_o = m["heads"] * m["hd"]
+    x = torch.randn(T, m["hidden"], generator=g, device="cuda", dtype=torch.float32).to(torch.bfloat16)
+
+    def forward(fused):
+        h, res = x, None
+        for (qkv, o, gate_up, down), (ln1, ln2) in zip(stack.layers, norms):
+            if fused:
+                if res is None:
+                    a, res = ln1.forward_quant(h, None, dtype), h
+                else:
+                    a, res = ln1.forward_quant(h, res, dtype)
+            else:
+                if res is None:
+                    a, res = ln1(h), h
+                else:
+                    a, res = ln1(h, res)
+            h = o(qkv(a)[:, :k_o])
+            if fused:
+                a, res = ln2.forward_quant(h, res, dtype)
+                h = down(act.forward_quant(gate_up(a), dtype))
+            else:
+                a, res = ln2(h, res)
+                h = down(act(gate_up(a)))
+        return h
+
+    out = {"tokens_per_step": T}
+    ys = {}
+    for name, fused in (("fused_producers", True), ("unfused", False)):
+        n0 = _ext.launch_count()
+        ys[name] = forward(fused)
+        launches = _ext.launch_count() - n0
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=s):
+                forward(fused)
+        torch.cuda.current_stream().wait_stream(s)
+        ms = time_steps(gr.replay, max(args.steps // 2, 5), 3, False)
+        out[name] = {"ms_per_step": ms, "value": T / (ms * 1e-3), "unit": "tokens/s",
+                     "gpu_launches_per_step": int(launches)}
+    out["same_bits"] = bool(torch.equal(ys["fused_producers"], ys["unfused"]))
+    assert out["same_bits"], "fused producers changed the result"
+    out["speedup"] = out["unfused"]["ms_per_step"] / out["fused_producers"]["ms_per_step"]
+    return out
+
+
 def fp8_group_leg(m, T, peaks, args):
     """BASELINE.json configs[2] / config 3 of SURVEY 8d: FP8-e4m3 weights with one scale per 128
     values of K (reference per_group_quant / per_group_matmul, quantization.py:194-234, 265-307), the
@@ -569,7 +636,7 @@ def main():
     ap.add_argument("--quant", default="per_row", choices=["per_row", "per_group"])
     ap.add_argument("--group-size", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-extra-legs", action="store_true", help="skip the FP8 g=128 leg")
+    ap.add_argument("--no-extra-legs", action="store_true", help="skip the FP8 g=128 and model-shaped legs")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
     ap.add_argument("--kernel-table", default=None, metavar="PATH",
                     help="AFTER the line is printed: replay 3 steps under the CUPTI kernel tracer and write "
@@ -743,8 +810,10 @@ def main():
         decode = decode_leg(stack, m, 16 * world, dtype, group, world, peaks, args, dist_on)
 
     # ---- FP8 g=128 leg (the reference's per-group configuration), default workload only
-    fp8_g128 = None
+    fp8_g128 = model_shaped = None
     if world == 1 and group == 0 and T_rank > 16 and args.model == "0.6b" and not args.no_extra_legs:
+        model_shaped = {"prefill": model_shaped_leg(stack, m, T, dtype, args),
+                        "decode": model_shaped_leg(stack, m, 16, dtype, args)}
         fp8_g128 = fp8_group_leg(m, T, peaks, args)
 
     # ---- dominant kernel alone (roofline): the GEMM (or GEMV for T <= 16) over all local weights
@@ -817,6 +886,8 @@ def main():
         line["decode"] = decode
     if fp8_g128 is not None:
         line["fp8_g128"] = fp8_g128
+    if model_shaped is not None:
+        line["model_shaped"] = model_shaped
     if tp_info is not None:
         line["tp_check"] = tp_info["status"]
         line["tp_collective"] = tp_info
