@@ -303,7 +303,8 @@ QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);
  * Every op is y = bf16((acc * sx[m]) * sw[n] + bias[n]) on per-token-quantised x, per-row weight
  * scales, exactly as ql_linear (INT8: bit-identical; FP8: fp32 summation order differs).
  *   ql_chain_workspace_bytes: device scratch the chain needs (0 = the chain is not supported:
- *     M > 16, K % 128, N % 8, K > 12288 ...);
+ *     M > 16, K % 128, N % 8, K > 12288 ...).  Two kernels: a tcgen05 consumer when every
+ *     K % 512 == 0, an mma.sync consumer otherwise (QL_CHAIN_TC=0 forces the latter);
  *   ql_chain_prepare: plans the chain for the current device (clusters of 4 CTAs, as many as
  *     cudaOccupancyMaxActiveClusters reports co-resident), encodes one TMA descriptor per op,
  *     writes descriptors and plan tables into `workspace` (256-byte aligned, stays owned by the

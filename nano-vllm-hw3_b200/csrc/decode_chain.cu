@@ -41,7 +41,8 @@
 // any order); FP8 per-row differs from the tcgen05 kernels only in fp32 summation order.
 //
 // OUTCOME: correct, and slower than one ql_linear per op on every Qwen3
-// stack measured (0.6B 7.2 vs 5.4 us per op, 8B 15.9 vs 12 us): the dependent chain release ->
+// stack measured (per op: 0.6B 6.2 us with the tcgen05 consumer below / 7.2 us with this mma.sync
+// one vs 5.4 us; 8B 14 / 15.9 vs 12 us): the dependent chain release ->
 // grid barrier -> activation read -> quantise -> first MMAs -> exchange -> epilogue costs ~10 000
 // cycles per op, more than a kernel boundary with programmatic dependent launch.  bench.py times
 // it next to the per-linear launches; nothing else in the engine depends on it.
@@ -540,28 +541,418 @@ __global__ void __launch_bounds__(kDcThreads, 1) decode_chain_kernel(const Chain
   cluster_wait();
 }
 
+// ------------------------------------------------------------------ tcgen05 form of the chain
+//
+// Same chain, same protocol (clusters of 4 split K, amax carried by the epilogue, one grid barrier
+// per op), but the consumer is the tensor core of gemm_skinny.cu: UMMA A = a 128-row weight tile
+// streamed by TMA in 128-byte K blocks (consecutive ring stages = consecutive K blocks of the same
+// rows: whole DRAM pages), UMMA B = this rank's K/4 slice of the 16 quantised tokens, written by
+// the quantiser threads straight into the 128B-swizzled K-major operand layout, accumulator
+// D[128 x 16] in TMEM (two buffers: the epilogue of tile i overlaps the MMAs of tile i+1).
+// Nothing of the weight stream passes through registers, so the consumer runs far above the HBM
+// rate and what the ring prefetched during the previous op's epilogue and the grid barrier is
+// consumed at once.  Split-K reduce-scatter over DSMEM: token columns 4r..4r+3 of every rank's
+// accumulator go to rank r (st.async, bytes counted on the receiver's mbarrier), which adds the
+// four partials in rank order, scales, stores bf16 and folds |y| into the next op's amax.
+// Requires K % 512 == 0 and K <= 12288 for every op (else the mma.sync kernel above is used).
+
+constexpr int kTcThreads = 384;                     // producer, MMA, 2 spare, 8 quantiser warps (4 of them the epilogue)
+constexpr int kTcAcc = 4;                           // accumulators per tile: the 4 MMAs of a K block go to 4 TMEM
+                                                    // tiles (a dependent M128 x N16 MMA costs ~140 cycles)
+constexpr int kTcStages = 10;
+constexpr int kTcStage = 128 * 128;                 // 16 KB: 128 weight rows x 128 B of K
+constexpr int kTcBres = 24 * 16 * 128;              // 48 KB: 16 tokens x 3072 B of K (K <= 12288)
+constexpr int kTcRecv = 4 * 128 * 16;               // 8 KB: [src rank][row][4 token columns] words
+constexpr int kTcSmall = 1024;
+constexpr int kTcSmem = kTcStages * kTcStage + kTcBres + kTcRecv + kTcSmall + 1024;
+static_assert(kTcSmem <= 227 * 1024, "tc chain shared memory");
+
+__device__ __forceinline__ void st_async_v4(uint32_t cluster_addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d,
+                                            uint32_t cluster_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(
+                   cluster_addr),
+               "r"(a), "r"(b), "r"(c), "r"(d), "r"(cluster_bar)
+               : "memory");
+}
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
+__device__ __forceinline__ void quant_sync() { asm volatile("bar.sync 3, 256;" ::: "memory"); }
+
+// tiles of 128 weight rows dealt to the clusters round robin, rotated per op
+__device__ __forceinline__ int tc_first_tile(int cluster, int NC, int rot) {
+  int q = cluster - rot;
+  if (q < 0) q += NC;
+  return q;
+}
+
+#define TC_TRACE(i)                                                                          \
+  do {                                                                                       \
+    if (p.trace != nullptr && e == 0 && l < 16)                                              \
+      p.trace[((size_t)cta * 16 + l) * 16 + (i)] = clock64();                                \
+  } while (0)
+
+template <int FMT>
+__global__ void __launch_bounds__(kTcThreads, 1) decode_chain_tc_kernel(const ChainParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* ring = smem;
+  uint8_t* bres = ring + kTcStages * kTcStage;
+  uint32_t* recv = reinterpret_cast<uint32_t*>(bres + kTcBres);
+  uint8_t* small = reinterpret_cast<uint8_t*>(recv) + kTcRecv;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(small);      // [10]
+  uint64_t* empty_bar = full_bar + kTcStages;                   // [10]
+  uint64_t* tfull_bar = empty_bar + kTcStages;                  // [2]
+  uint64_t* tempty_bar = tfull_bar + 2;                         // [2]
+  uint64_t* bready_bar = tempty_bar + 2;
+  uint64_t* recv_bar = bready_bar + 1;
+  uint64_t* free_bar = recv_bar + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(free_bar + 1);
+  float* sx_s = reinterpret_cast<float*>(small + 256);          // [16]
+  int* amax_s = reinterpret_cast<int*>(small + 320);            // [16]
+  uint32_t* flag_s = reinterpret_cast<uint32_t*>(small + 384);
+  ChainOp* desc_s = reinterpret_cast<ChainOp*>(small + 512);    // [3]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int G = gridDim.x, cta = blockIdx.x;
+  const int rank = (int)cluster_ctarank(), cluster = cta / kDcC;
+  constexpr float qmax = Fmt<FMT>::qmax;
+
+  if (tid == 0) {
+    for (int i = 0; i < kTcStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 4);
+    }
+    mbar_init(bready_bar, 8);
+    mbar_init(recv_bar, 1);
+    mbar_init(free_bar, kDcC);
+    mbar_fence_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 2 * kTcAcc * 16);
+    tmem_relinquish();
+  }
+  if (tid >= 64 && tid < 80 && ((tid - 64) >> 3) < p.n_ops)
+    reinterpret_cast<uint4*>(desc_s)[tid - 64] = __ldg(reinterpret_cast<const uint4*>(p.ops) + (tid - 64));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  cluster_arrive();
+  cluster_wait();
+
+  if (warp == 0) {
+    // ===================== TMA producer: every op's weight tiles, as far ahead as the ring allows ==
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int N = __ldg(&p.ops[0].N), K = __ldg(&p.ops[0].K), rot = __ldg(&p.ops[0].rot);
+      tma_prefetch_desc(p.tmaps);
+      for (int l = 0; l < p.n_ops; ++l) {
+        const int tiles = (N + 127) >> 7, nkb = K >> 9;          // K / 4 ranks / 128 B
+        const int t0 = tc_first_tile(cluster, p.NC, rot);
+        const CUtensorMap* tm = p.tmaps + l;
+        if (l + 1 < p.n_ops) {
+          N = __ldg(&p.ops[l + 1].N); K = __ldg(&p.ops[l + 1].K); rot = __ldg(&p.ops[l + 1].rot);
+          tma_prefetch_desc(p.tmaps + l + 1);
+        }
+        for (int tile = t0; tile < tiles; tile += p.NC) {
+          for (int kb = 0; kb < nkb; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            mbar_expect_tx(&full_bar[stage], kTcStage);
+            tma_load_2d(ring + stage * kTcStage, tm, &full_bar[stage], (rank * nkb + kb) * 128, tile * 128, kEvictFirst);
+            if (p.trace != nullptr && l < 16 && tile == t0 && (kb == 0 || kb == nkb - 1))
+              p.trace[((size_t)cta * 16 + l) * 16 + (kb == 0 ? 14 : 15)] = clock64();
+            if (++stage == kTcStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer ==========================================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc<FMT>(128, 16);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0, b_phase = 0;
+      int N = __ldg(&p.ops[0].N), K = __ldg(&p.ops[0].K), rot = __ldg(&p.ops[0].rot);
+      for (int l = 0; l < p.n_ops; ++l) {
+        const int tiles = (N + 127) >> 7, nkb = K >> 9;
+        const int t0 = tc_first_tile(cluster, p.NC, rot);
+        if (l + 1 < p.n_ops) {
+          N = __ldg(&p.ops[l + 1].N); K = __ldg(&p.ops[l + 1].K); rot = __ldg(&p.ops[l + 1].rot);
+        }
+        if (t0 >= tiles) continue;
+        mbar_wait(bready_bar, b_phase);                 // this op's activations are quantised into bres
+        b_phase ^= 1;
+        tc_fence_after();
+        if (p.trace != nullptr && l < 16) p.trace[((size_t)cta * 16 + l) * 16 + 11] = clock64();
+        for (int tile = t0; tile < tiles; tile += p.NC) {
+          mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * (kTcAcc * 16);
+          for (int kb = 0; kb < nkb; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            if (p.trace != nullptr && l < 16 && tile == t0 && (kb == 0 || kb == nkb - 1))
+              p.trace[((size_t)cta * 16 + l) * 16 + (kb == 0 ? 12 : 13)] = clock64();
+            const uint64_t a_desc = make_sw128_kmajor_desc(smem_u32(ring + stage * kTcStage));
+            const uint64_t b_desc = make_sw128_kmajor_desc(smem_u32(bres) + kb * (16 * 128));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              if constexpr (FMT == QL_INT8) mma_i8(d_tmem + k * 16, a_desc + 2 * k, b_desc + 2 * k, idesc, kb > 0);
+              else mma_f8(d_tmem + k * 16, a_desc + 2 * k, b_desc + 2 * k, idesc, kb > 0);
+            }
+            tc_commit(&empty_bar[stage]);
+            if (++stage == kTcStages) { stage = 0; phase ^= 1; }
+          }
+          tc_commit(&tfull_bar[acc]);
+          if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===================== quantiser (256 threads: warps 4-11) + epilogue (warps 4-7) ============
+    const int e = tid - 128;                       // 0..255
+    const int q = (warp - 4) & 3;                  // TMEM lane quarter of an epilogue warp (= warp % 4)
+    const bool epi = warp < 8;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t recv_local = smem_u32(recv), recv_bar_local = smem_u32(recv_bar),
+                   free_bar_local = smem_u32(free_bar);
+    int acc = 0;
+    uint32_t acc_phase = 0, n_exch = 0;
+
+    for (int l = 0; l < p.n_ops; ++l) {
+      const ChainOp& op = desc_s[l % 3];
+      const int N = op.N, K = op.K;
+      const int tiles = (N + 127) >> 7, nkb = K >> 9;
+      const int t0 = tc_first_tile(cluster, p.NC, op.rot);
+      uint4 dpre = make_uint4(0, 0, 0, 0);
+      if (e < 8 && l + 2 < p.n_ops) dpre = __ldg(reinterpret_cast<const uint4*>(p.ops + l + 2) + e);
+      TC_TRACE(0);
+
+      if (t0 < tiles) {
+        const int64_t ldx = op.ldx, ldy = op.ldy;
+        const float* sw = op.sw;
+        const uint16_t* bias = op.bias;
+        uint16_t* y = op.y;
+        const int amax_cols = op.amax_cols;
+
+        // ---- this rank's K/4 slice of the activation: read, quantise into the UMMA B layout --------
+        // item = 16 consecutive K values of one token (one 16-byte chunk of a swizzled 128-byte B row)
+        const int nit = nkb * 8;                       // items per token
+        const int items = 16 * nit;
+        const uint16_t* xk = op.x + (size_t)rank * nkb * 128;
+        uint4 xv[4][2];
+        auto load_items = [&](int base) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int it = base + i * 256 + e;
+            const int m = it / nit, ii = it - m * nit;
+            xv[i][0] = xv[i][1] = make_uint4(0, 0, 0, 0);
+            if (it < items && m < p.M) {
+              const uint4* s = reinterpret_cast<const uint4*>(xk + (size_t)m * ldx + ii * 16);
+              xv[i][0] = __ldcg(s);
+              xv[i][1] = __ldcg(s + 1);
+            }
+          }
+        };
+        load_items(0);
+        if (op.x_amax) {
+          if (e < 16) amax_s[e] = (int)__ldcg(p.amax + l * 16 + e);
+        } else {
+          if (e < 16) amax_s[e] = 0;
+          quant_sync();
+          const int nvec = K >> 3;
+          for (int m = warp - 4; m < p.M; m += 8) {
+            float a = 0.0f;
+            const uint4* row = reinterpret_cast<const uint4*>(op.x + (size_t)m * ldx);
+            for (int i = lane; i < nvec; i += 32) a = fmaxf(a, amax8(__ldcg(row + i)));
+            a = warp_max(a);
+            if (lane == 0) amax_s[m] = __float_as_int(a);
+          }
+        }
+        quant_sync();
+        TC_TRACE(1);
+        if (e < 16) sx_s[e] = __fdiv_rn(fmaxf(__int_as_float(amax_s[e]), 1e-8f), qmax);
+        for (int base = 0; base < items; base += 4 * 256) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int it = base + i * 256 + e;
+            if (it < items) {
+              const int m = it / nit, ii = it - m * nit;
+              const float inv = __fdiv_rn(qmax, fmaxf(__int_as_float(amax_s[m]), 1e-8f));
+              const uint2 q0 = quant8_mul<FMT>(xv[i][0], inv), q1 = quant8_mul<FMT>(xv[i][1], inv);
+              uint8_t* dst = bres + (ii >> 3) * (16 * 128) + (m >> 3) * 1024 + (m & 7) * 128 + (((ii & 7) ^ (m & 7)) << 4);
+              *reinterpret_cast<uint4*>(dst) = make_uint4(q0.x, q0.y, q1.x, q1.y);
+            }
+          }
+          if (base + 4 * 256 < items) load_items(base + 4 * 256);
+        }
+        quant_sync();                                  // every thread is done with this op's input amax
+        if (e < 16) amax_s[e] = 0;                     // from here on: running max of |y| for the next op
+        fence_proxy_async_smem();
+        quant_sync();
+        if (lane == 0) mbar_arrive(bready_bar);
+        TC_TRACE(2);
+
+        if (epi) {
+          for (int tile = t0; tile < tiles; tile += p.NC) {
+            const int n = tile * 128 + q * 32 + lane;    // the weight row on this thread's TMEM lane
+            const bool n_ok = n < N;
+            const float swn = n_ok ? __ldg(sw + n) : 0.0f;
+            const float bn = (n_ok && bias != nullptr) ? bf16_lo(__ldg(bias + n)) : 0.0f;
+            if (e == 0) mbar_expect_tx(recv_bar, kTcRecv);
+            mbar_wait(&tfull_bar[acc], acc_phase);
+            tc_fence_after();
+            if (tile == t0) TC_TRACE(3);
+            // the tile's kTcAcc partial accumulators (one per 32-byte K step of a block): add them
+            uint32_t r[16];
+            {
+              uint32_t r1[16], r2[16], r3[16];
+              const uint32_t ta = lane_addr + acc * (kTcAcc * 16);
+              tmem_ld16(ta, r);
+              tmem_ld16(ta + 16, r1);
+              tmem_ld16(ta + 32, r2);
+              tmem_ld16(ta + 48, r3);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 16; ++i) {
+                if constexpr (FMT == QL_INT8) {
+                  r[i] = (uint32_t)((int)r[i] + (int)r1[i] + (int)r2[i] + (int)r3[i]);
+                } else {
+                  const float s01 = __fadd_rn(__uint_as_float(r[i]), __uint_as_float(r1[i]));
+                  const float s23 = __fadd_rn(__uint_as_float(r2[i]), __uint_as_float(r3[i]));
+                  r[i] = __float_as_uint(__fadd_rn(s01, s23));
+                }
+              }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            // reduce-scatter: token columns 4d..4d+3 of this row go to rank d
+            if (n_exch > 0) mbar_wait(free_bar, (n_exch - 1) & 1u);
+            const uint32_t off = (uint32_t)((rank * 128 + q * 32 + lane) * 16);
+#pragma unroll
+            for (int d = 0; d < kDcC; ++d)
+              st_async_v4(mapa_u32(recv_local + off, (uint32_t)d), r[4 * d], r[4 * d + 1], r[4 * d + 2], r[4 * d + 3],
+                          mapa_u32(recv_bar_local, (uint32_t)d));
+            mbar_wait(recv_bar, n_exch & 1u);
+            if (tile == t0) TC_TRACE(4);
+            uint4 sum = *reinterpret_cast<const uint4*>(recv + (q * 32 + lane) * 4);
+#pragma unroll
+            for (int s = 1; s < kDcC; ++s) {
+              const uint4 o = *reinterpret_cast<const uint4*>(recv + (s * 128 + q * 32 + lane) * 4);
+              if constexpr (FMT == QL_INT8) {
+                sum.x += o.x; sum.y += o.y; sum.z += o.z; sum.w += o.w;
+              } else {
+                sum.x = __float_as_uint(__fadd_rn(__uint_as_float(sum.x), __uint_as_float(o.x)));
+                sum.y = __float_as_uint(__fadd_rn(__uint_as_float(sum.y), __uint_as_float(o.y)));
+                sum.z = __float_as_uint(__fadd_rn(__uint_as_float(sum.z), __uint_as_float(o.z)));
+                sum.w = __float_as_uint(__fadd_rn(__uint_as_float(sum.w), __uint_as_float(o.w)));
+              }
+            }
+            const uint32_t raw[4] = {sum.x, sum.y, sum.z, sum.w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const int m = rank * 4 + c;
+              float mx = 0.0f;
+              if (m < p.M && n_ok) {
+                const float a = FMT == QL_INT8 ? __int2float_rn((int)raw[c]) : __uint_as_float(raw[c]);
+                float v = __fmul_rn(__fmul_rn(a, sx_s[m]), swn);              // (acc * sa) * sb, reference :121
+                if (bias != nullptr) v = __fadd_rn(v, bn);
+                const uint16_t o = f2bf(v);
+                y[(size_t)m * ldy + n] = o;
+                if (n < amax_cols) mx = fabsf(bf16_lo(o));
+              }
+              if (amax_cols > 0 && m < p.M) {
+                mx = warp_max(mx);
+                if (lane == 0 && mx > 0.0f) atomicMax(amax_s + m, __float_as_int(mx));
+              }
+            }
+            epi_sync();
+            if (e < kDcC) mbar_arrive_relaxed_cluster(mapa_u32(free_bar_local, (uint32_t)e));
+            ++n_exch;
+          }
+          if (amax_cols > 0 && e < 16 && e < p.M && amax_s[e] > 0)
+            atomicMax(reinterpret_cast<int*>(p.amax) + (l + 1) * 16 + e, amax_s[e]);
+          TC_TRACE(7);
+        }
+      }
+
+      // ---- grid barrier (the epilogue warps; the helper quantiser warps wait at the 256-thread sync) --
+      if (l + 1 < p.n_ops) {
+        if (e < 8 && l + 2 < p.n_ops) reinterpret_cast<uint4*>(desc_s + (l + 2) % 3)[e] = dpre;
+        if (epi) {
+          epi_sync();                // orders the epilogue threads' stores / atomics before the release
+          TC_TRACE(8);
+          if (e == 0) {
+            red_release_gpu_add(p.sync, 1u);
+            TC_TRACE(9);
+            const uint32_t target = (uint32_t)(l + 1) * (uint32_t)G;
+            if (ld_acquire_gpu(p.sync) < target) {
+              const uint64_t t0g = globaltimer_ns();
+              while (ld_acquire_gpu(p.sync) < target)
+                if (globaltimer_ns() - t0g > 4000000000ull) __trap();
+            }
+            TC_TRACE(10);
+          }
+        }
+        quant_sync();
+      }
+    }
+
+    quant_sync();
+    if (e == 0) {
+      __threadfence();
+      *flag_s = atomicAdd(p.sync + 1, 1u) == (uint32_t)(G - 1);
+    }
+    quant_sync();
+    if (*flag_s) {
+      for (int i = e; i < p.n_ops * 16; i += 256) p.amax[i] = 0u;
+      if (e == 0) {
+        p.sync[0] = 0u;
+        p.sync[1] = 0u;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_arrive();
+  cluster_wait();
+  if (warp == 2) tmem_dealloc(tmem_base, 2 * kTcAcc * 16);
+}
+
 // ------------------------------------------------------------------ host side
 
 struct ChainPlanHost {      // what ql_chain_run needs; lives in the caller's ql_chain_plan blob
   uint32_t magic;
   int n_ops, M, fmt, clusters, smem, cooperative;
+  int tc;                   // 1: tcgen05 kernel (every K % 512 == 0, K <= 12288), 0: mma.sync kernel
   size_t off_amax, off_ops, off_tmaps, total;
 };
 static_assert(sizeof(ChainPlanHost) <= sizeof(ql_chain_plan), "ql_chain_plan too small");
 
 static size_t rup(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-static const void* chain_kernel(int fmt) {
+static const void* chain_kernel(int fmt, int tc) {
+  if (tc)
+    return fmt == QL_INT8 ? reinterpret_cast<const void*>(decode_chain_tc_kernel<QL_INT8>)
+                          : reinterpret_cast<const void*>(decode_chain_tc_kernel<QL_FP8_E4M3>);
   return fmt == QL_INT8 ? reinterpret_cast<const void*>(decode_chain_kernel<QL_INT8>)
                         : reinterpret_cast<const void*>(decode_chain_kernel<QL_FP8_E4M3>);
 }
 
 static void chain_launch_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, int clusters, int cooperative,
-                             cudaStream_t st) {
+                             cudaStream_t st, int tc) {
   memset(cfg, 0, sizeof(*cfg));
   cfg->gridDim = dim3((unsigned)(clusters * kDcC));
-  cfg->blockDim = dim3(kDcThreads);
-  cfg->dynamicSmemBytes = (size_t)kDcSmem;
+  cfg->blockDim = dim3(tc ? kTcThreads : kDcThreads);
+  cfg->dynamicSmemBytes = (size_t)(tc ? kTcSmem : kDcSmem);
   cfg->stream = st;
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kDcC;
@@ -575,19 +966,19 @@ static void chain_launch_cfg(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr,
 
 // Clusters of kDcC CTAs (one CTA per SM: ~220 KB of shared memory each) the device can hold at once.
 // Every CTA spins on the grid barrier, so the grid must never exceed this.
-static int chain_max_clusters(int fmt) {
-  static int cached[64][2];
+static int chain_max_clusters(int fmt, int tc) {
+  static int cached[64][4];
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
-  const int f = fmt == QL_INT8 ? 0 : 1;
+  const int f = (fmt == QL_INT8 ? 0 : 1) + 2 * (tc ? 1 : 0);
   if (cached[dev][f] > 0) return cached[dev][f];
-  static SmemAttrOnce once_i8, once_f8;
-  if (ensure_max_smem(chain_kernel(fmt), kDcSmem, fmt == QL_INT8 ? once_i8 : once_f8)) return 0;
+  static SmemAttrOnce once[4];
+  if (ensure_max_smem(chain_kernel(fmt, tc), tc ? kTcSmem : kDcSmem, once[f])) return 0;
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr[2];
-  chain_launch_cfg(&cfg, attr, num_sms() / kDcC, 0, nullptr);
+  chain_launch_cfg(&cfg, attr, num_sms() / kDcC, 0, nullptr, tc);
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, chain_kernel(fmt), &cfg) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveClusters(&n, chain_kernel(fmt, tc), &cfg) != cudaSuccess) {
     (void)cudaGetLastError();
     return 0;
   }
@@ -600,8 +991,17 @@ static int chain_max_clusters(int fmt) {
   return n;
 }
 
+// every op fits the tcgen05 kernel?  (QL_CHAIN_TC=0 forces the mma.sync kernel)
+static int chain_wants_tc(const ql_chain_op* ops, int n_ops) {
+  const char* e = getenv("QL_CHAIN_TC");
+  if (e != nullptr && e[0] == '0') return 0;
+  for (int l = 0; l < n_ops; ++l)
+    if (ops[l].K % 512 != 0 || ops[l].K > 12288) return 0;
+  return 1;
+}
+
 static int plan_chain(const ql_chain_op* ops, int n_ops, int64_t M, int clusters, ChainPlanHost* pl, ChainOp* dev_ops,
-                      CUtensorMap* tmaps) {
+                      CUtensorMap* tmaps, int tc) {
   if (ops == nullptr || n_ops <= 0 || n_ops > 4096 || M <= 0 || M > 16) return QL_ERR_BAD_SHAPE;
   for (int l = 0; l < n_ops; ++l) {
     const ql_chain_op& o = ops[l];
@@ -644,15 +1044,19 @@ static int plan_chain(const ql_chain_op* ops, int n_ops, int64_t M, int clusters
       d.rot = clusters > 0 ? (int)(((int64_t)l * 11) % clusters) : 0;   // spread the one-group-longer units
       d.x_amax = chained ? 1 : 0;
       d.amax_cols = (l + 1 < n_ops && ops[l + 1].x == nullptr) ? (int)ops[l + 1].K : 0;
-      if (!make_tmap_2d_plain(&tmaps[l], o.qw, CU_TENSOR_MAP_DATA_TYPE_UINT32, o.K / 4, o.N, o.K, cb * 16, 8))
+      if (tc) {
+        if (!make_tmap_2d(&tmaps[l], o.qw, CU_TENSOR_MAP_DATA_TYPE_UINT8, o.K, o.N, o.K, 128, 128)) return QL_ERR_CUDA;
+      } else if (!make_tmap_2d_plain(&tmaps[l], o.qw, CU_TENSOR_MAP_DATA_TYPE_UINT32, o.K / 4, o.N, o.K, cb * 16, 8)) {
         return QL_ERR_CUDA;
+      }
     }
   }
   pl->magic = kDcMagic;
   pl->n_ops = n_ops;
   pl->M = (int)M;
   pl->clusters = clusters;
-  pl->smem = kDcSmem;
+  pl->smem = tc ? kTcSmem : kDcSmem;
+  pl->tc = tc;
   pl->off_amax = 256;
   pl->off_ops = pl->off_amax + rup((size_t)n_ops * 64, 256);
   pl->off_tmaps = pl->off_ops + rup((size_t)n_ops * sizeof(ChainOp), 256);
@@ -668,7 +1072,7 @@ extern "C" {
 
 size_t ql_chain_workspace_bytes(const ql_chain_op* ops, int n_ops, int64_t M) {
   ChainPlanHost pl;
-  if (plan_chain(ops, n_ops, M, 0, &pl, nullptr, nullptr) != QL_OK) return 0;
+  if (plan_chain(ops, n_ops, M, 0, &pl, nullptr, nullptr, 0) != QL_OK) return 0;
   return pl.total;
 }
 
@@ -679,7 +1083,9 @@ int ql_chain_prepare(const ql_chain_op* ops, int n_ops, int64_t M, int fmt, int6
   if (plan == nullptr || workspace == nullptr) return QL_ERR_NULL;
   if (reinterpret_cast<uintptr_t>(workspace) & 255) return QL_ERR_MISALIGNED;
   if (int e = ql_device_check()) return e;
-  const int clusters = chain_max_clusters(fmt);
+  if (ops == nullptr || n_ops <= 0) return QL_ERR_BAD_SHAPE;
+  const int tc = chain_wants_tc(ops, n_ops);
+  const int clusters = chain_max_clusters(fmt, tc);
   if (clusters <= 0) return QL_ERR_CUDA;
   ChainPlanHost pl;
   const size_t nn = (size_t)(n_ops > 0 ? n_ops : 1);
@@ -690,7 +1096,7 @@ int ql_chain_prepare(const ql_chain_op* ops, int n_ops, int64_t M, int fmt, int6
     free(host_tm);
     return QL_ERR_CUDA;
   }
-  int e = plan_chain(ops, n_ops, M, clusters, &pl, host_ops, host_tm);
+  int e = plan_chain(ops, n_ops, M, clusters, &pl, host_ops, host_tm, tc);
   if (e == QL_OK && workspace_bytes < pl.total) e = QL_ERR_WORKSPACE;
   if (e == QL_OK) {
     pl.fmt = fmt;
@@ -731,7 +1137,7 @@ int ql_chain_run(const ql_chain_plan* plan, void* workspace, ql_stream_t stream)
   p.sync = reinterpret_cast<uint32_t*>(ws);
   p.amax = reinterpret_cast<uint32_t*>(ws + pl.off_amax);
   p.trace = skinny_trace_ptr();
-  const void* kern = chain_kernel(pl.fmt);
+  const void* kern = chain_kernel(pl.fmt, pl.tc);
   // every CTA spins on the grid barrier: the grid must be co-resident.  Cooperative launch makes the
   // driver check that; where it refuses the cluster + cooperative combination the grid is still
   // sized by cudaOccupancyMaxActiveClusters (chain_max_clusters) and the barrier spin is bounded.
@@ -741,7 +1147,7 @@ int ql_chain_run(const ql_chain_plan* plan, void* workspace, ql_stream_t stream)
   void* args[] = {&p};
   cudaError_t err = cudaErrorUnknown;
   if (coop_ok) {
-    chain_launch_cfg(&cfg, attr, pl.clusters, 1, (cudaStream_t)stream);
+    chain_launch_cfg(&cfg, attr, pl.clusters, 1, (cudaStream_t)stream, pl.tc);
     err = cudaLaunchKernelExC(&cfg, kern, args);
     if (err != cudaSuccess) {
       if (getenv("QL_DEBUG") != nullptr)
@@ -752,7 +1158,7 @@ int ql_chain_run(const ql_chain_plan* plan, void* workspace, ql_stream_t stream)
     }
   }
   if (!coop_ok) {
-    chain_launch_cfg(&cfg, attr, pl.clusters, 0, (cudaStream_t)stream);
+    chain_launch_cfg(&cfg, attr, pl.clusters, 0, (cudaStream_t)stream, pl.tc);
     err = cudaLaunchKernelExC(&cfg, kern, args);
   }
   count_launch();

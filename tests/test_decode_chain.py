@@ -25,6 +25,15 @@ QWEN8 = [(6144, 4096), (4096, 4096), (24576, 4096), (4096, 12288)]
 ODD = [(264, 384), (128, 256), (1032, 128), (8, 1024)]
 
 
+@pytest.fixture(params=["tcgen05", "mma_sync"], autouse=True)
+def chain_kernel(request, monkeypatch):
+    """Both forms of the chain: decode_chain_tc_kernel (every K % 512 == 0; the default) and
+    decode_chain_kernel (mma.sync; also the fallback for other K).  QL_CHAIN_TC is read by
+    ql_chain_prepare."""
+    monkeypatch.setenv("QL_CHAIN_TC", "1" if request.param == "tcgen05" else "0")
+    return request.param
+
+
 def make_ops(shapes, M, fmt, seed, own=(), bias_at=(), x_stride_pad=0):
     from nanovllm import _ext
     g = torch.Generator(device="cuda").manual_seed(seed)

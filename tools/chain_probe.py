@@ -54,10 +54,13 @@ torch.cuda.synchronize()
 _ext.load().ql_debug_set_trace(None)
 t = tr.view(G, 16, 16).cpu().double()
 print("per-op cycles from op start, median over stamping CTAs (max in brackets)")
-print("stamps: " + ", ".join(f"{i}={n}" for i, n in enumerate(lab)))
+print("stamps (mma.sync kernel): " + ", ".join(f"{i}={n}" for i, n in enumerate(lab)))
+print("stamps (tcgen05 kernel): 0=start, 1=amax sync, 2=B operand quantised, 3=first tile accumulated, 4=first partials landed, "
+      "7=op finished, 8=pre-arrive sync, 9=arrived, 10=barrier done, 11=MMA warp: B ready, 12/13=first / last K block of the "
+      "first tile in shared memory, 14/15=TMA of those blocks issued (negative = before the op started)")
 for l in range(min(16, len(ops))):
     row = []
-    for i in range(1, 11):
+    for i in range(1, 16):
         ok = (t[:, l, i] > 0) & (t[:, l, 0] > 0)
         v = (t[:, l, i] - t[:, l, 0])[ok]
         row.append("    -    " if v.numel() == 0 else f"{v.median():5.0f}[{v.max():5.0f}]")
