@@ -41,8 +41,8 @@
 // any order); FP8 per-row differs from the tcgen05 kernels only in fp32 summation order.
 //
 // OUTCOME: correct, and slower than one ql_linear per op on every Qwen3
-// stack measured (per op: 0.6B 6.2 us with the tcgen05 consumer below / 7.2 us with this mma.sync
-// one vs 5.4 us; 8B 14 / 15.9 vs 12 us): the dependent chain release ->
+// stack measured (per op: 0.6B 5.8 us with the tcgen05 consumer below / 7.2 us with this mma.sync
+// one vs 5.4 us; 8B 13.4 / 15.9 vs 12 us): the dependent chain release ->
 // grid barrier -> activation read -> quantise -> first MMAs -> exchange -> epilogue costs ~10 000
 // cycles per op, more than a kernel boundary with programmatic dependent launch.  bench.py times
 // it next to the per-linear launches; nothing else in the engine depends on it.
@@ -563,6 +563,7 @@ constexpr int kTcStages = 10;
 constexpr int kTcStage = 128 * 128;                 // 16 KB: 128 weight rows x 128 B of K
 constexpr int kTcBres = 24 * 16 * 128;              // 48 KB: 16 tokens x 3072 B of K (K <= 12288)
 constexpr int kTcRecv = 4 * 128 * 16;               // 8 KB: [src rank][row][4 token columns] words
+constexpr int kTcBGroups = 6;                       // B-operand readiness is signalled per 4 K blocks (24 / 4)
 constexpr int kTcSmall = 1024;
 constexpr int kTcSmem = kTcStages * kTcStage + kTcBres + kTcRecv + kTcSmall + 1024;
 static_assert(kTcSmem <= 227 * 1024, "tc chain shared memory");
@@ -602,13 +603,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) decode_chain_tc_kernel(const Ch
   uint64_t* empty_bar = full_bar + kTcStages;                   // [10]
   uint64_t* tfull_bar = empty_bar + kTcStages;                  // [2]
   uint64_t* tempty_bar = tfull_bar + 2;                         // [2]
-  uint64_t* bready_bar = tempty_bar + 2;
-  uint64_t* recv_bar = bready_bar + 1;
+  uint64_t* bready_bar = tempty_bar + 2;                        // [6]: groups of 4 K blocks of the B operand
+  uint64_t* recv_bar = bready_bar + kTcBGroups;
   uint64_t* free_bar = recv_bar + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(free_bar + 1);
-  float* sx_s = reinterpret_cast<float*>(small + 256);          // [16]
-  int* amax_s = reinterpret_cast<int*>(small + 320);            // [16]
-  uint32_t* flag_s = reinterpret_cast<uint32_t*>(small + 384);
+  float* sx_s = reinterpret_cast<float*>(small + 320);          // [16]
+  int* amax_s = reinterpret_cast<int*>(small + 384);            // [16]
+  uint32_t* flag_s = reinterpret_cast<uint32_t*>(small + 448);
   ChainOp* desc_s = reinterpret_cast<ChainOp*>(small + 512);    // [3]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -625,7 +626,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) decode_chain_tc_kernel(const Ch
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], 4);
     }
-    mbar_init(bready_bar, 8);
+    for (int i = 0; i < kTcBGroups; ++i) mbar_init(&bready_bar[i], 8);
     mbar_init(recv_bar, 1);
     mbar_init(free_bar, kDcC);
     mbar_fence_init();
@@ -676,7 +677,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) decode_chain_tc_kernel(const Ch
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc<FMT>(128, 16);
       int stage = 0, acc = 0;
-      uint32_t phase = 0, acc_phase = 0, b_phase = 0;
+      uint32_t phase = 0, acc_phase = 0, b_phases = 0;   // b_phases: one parity bit per B-operand group
       int N = __ldg(&p.ops[0].N), K = __ldg(&p.ops[0].K), rot = __ldg(&p.ops[0].rot);
       for (int l = 0; l < p.n_ops; ++l) {
         const int tiles = (N + 127) >> 7, nkb = K >> 9;
@@ -685,15 +686,21 @@ __global__ void __launch_bounds__(kTcThreads, 1) decode_chain_tc_kernel(const Ch
           N = __ldg(&p.ops[l + 1].N); K = __ldg(&p.ops[l + 1].K); rot = __ldg(&p.ops[l + 1].rot);
         }
         if (t0 >= tiles) continue;
-        mbar_wait(bready_bar, b_phase);                 // this op's activations are quantised into bres
-        b_phase ^= 1;
-        tc_fence_after();
-        if (p.trace != nullptr && l < 16) p.trace[((size_t)cta * 16 + l) * 16 + 11] = clock64();
+        // (the B operand becomes ready group by group: see the quantiser)
         for (int tile = t0; tile < tiles; tile += p.NC) {
           mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * (kTcAcc * 16);
           for (int kb = 0; kb < nkb; ++kb) {
+            if (tile == t0 && (kb & 3) == 0) {
+              // K blocks kb..kb+3 of this op's activations are quantised into bres (the quantiser
+              // works through the slice in K order while the first blocks are already multiplied)
+              const int gi = kb >> 2;
+              mbar_wait(&bready_bar[gi], (b_phases >> gi) & 1u);
+              b_phases ^= 1u << gi;
+              tc_fence_after();
+              if (kb == 0 && p.trace != nullptr && l < 16) p.trace[((size_t)cta * 16 + l) * 16 + 11] = clock64();
+            }
             mbar_wait(&full_bar[stage], phase);
             tc_fence_after();
             if (p.trace != nullptr && l < 16 && tile == t0 && (kb == 0 || kb == nkb - 1))
@@ -742,25 +749,29 @@ __global__ void __launch_bounds__(kTcThreads, 1) decode_chain_tc_kernel(const Ch
         const int amax_cols = op.amax_cols;
 
         // ---- this rank's K/4 slice of the activation: read, quantise into the UMMA B layout --------
-        // item = 16 consecutive K values of one token (one 16-byte chunk of a swizzled 128-byte B row)
-        const int nit = nkb * 8;                       // items per token
-        const int items = 16 * nit;
+        // item = 16 consecutive K values of one token (one 16-byte chunk of a swizzled 128-byte B
+        // row), ordered K-block-major: it = (kb * 16 + token) * 8 + chunk.  The slice is processed
+        // in groups of 4 K blocks (512 items, 2 per thread) and every group is published to the MMA
+        // warp on its own barrier, so the first K blocks are being multiplied (their weights are
+        // already in the ring) while the rest of the slice is still being quantised.
+        const int items = nkb * 128;
+        const int ngroups = (nkb + 3) >> 2;
         const uint16_t* xk = op.x + (size_t)rank * nkb * 128;
-        uint4 xv[4][2];
-        auto load_items = [&](int base) {
+        uint4 xa[2][2], xb[2][2];                       // two groups in flight: [item][vector]
+        auto load_group = [&](int gi, uint4 (&xv)[2][2]) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int it = base + i * 256 + e;
-            const int m = it / nit, ii = it - m * nit;
+          for (int i = 0; i < 2; ++i) {
+            const int it = gi * 512 + i * 256 + e;
+            const int m = (it >> 3) & 15;
             xv[i][0] = xv[i][1] = make_uint4(0, 0, 0, 0);
             if (it < items && m < p.M) {
-              const uint4* s = reinterpret_cast<const uint4*>(xk + (size_t)m * ldx + ii * 16);
+              const uint4* s = reinterpret_cast<const uint4*>(xk + (size_t)m * ldx + ((it >> 7) * 8 + (it & 7)) * 16);
               xv[i][0] = __ldcg(s);
               xv[i][1] = __ldcg(s + 1);
             }
           }
         };
-        load_items(0);
+        load_group(0, xa);
         if (op.x_amax) {
           if (e < 16) amax_s[e] = (int)__ldcg(p.amax + l * 16 + e);
         } else {
@@ -778,25 +789,33 @@ __global__ void __launch_bounds__(kTcThreads, 1) decode_chain_tc_kernel(const Ch
         quant_sync();
         TC_TRACE(1);
         if (e < 16) sx_s[e] = __fdiv_rn(fmaxf(__int_as_float(amax_s[e]), 1e-8f), qmax);
-        for (int base = 0; base < items; base += 4 * 256) {
+        // quantise group gi from `cur` while group gi + 1 is being loaded into `nxt`, then publish it
+        auto do_group = [&](int gi, uint4 (&cur)[2][2], uint4 (&nxt)[2][2]) {
+          if (gi + 1 < ngroups) load_group(gi + 1, nxt);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int it = base + i * 256 + e;
+          for (int i = 0; i < 2; ++i) {
+            const int it = gi * 512 + i * 256 + e;
             if (it < items) {
-              const int m = it / nit, ii = it - m * nit;
+              const int m = (it >> 3) & 15, c = it & 7, kb = it >> 7;
               const float inv = __fdiv_rn(qmax, fmaxf(__int_as_float(amax_s[m]), 1e-8f));
-              const uint2 q0 = quant8_mul<FMT>(xv[i][0], inv), q1 = quant8_mul<FMT>(xv[i][1], inv);
-              uint8_t* dst = bres + (ii >> 3) * (16 * 128) + (m >> 3) * 1024 + (m & 7) * 128 + (((ii & 7) ^ (m & 7)) << 4);
+              const uint2 q0 = quant8_mul<FMT>(cur[i][0], inv), q1 = quant8_mul<FMT>(cur[i][1], inv);
+              uint8_t* dst = bres + kb * (16 * 128) + (m >> 3) * 1024 + (m & 7) * 128 + ((c ^ (m & 7)) << 4);
               *reinterpret_cast<uint4*>(dst) = make_uint4(q0.x, q0.y, q1.x, q1.y);
             }
           }
-          if (base + 4 * 256 < items) load_items(base + 4 * 256);
+          if (gi + 1 == ngroups) {
+            quant_sync();                                // every thread is done with this op's input amax
+            if (e < 16) amax_s[e] = 0;                   // from here on: running max of |y| for the next op
+          }
+          fence_proxy_async_smem();
+          quant_sync();
+          if (lane == 0) mbar_arrive(&bready_bar[gi]);
+        };
+#pragma unroll 1
+        for (int gi = 0; gi < ngroups; gi += 2) {
+          do_group(gi, xa, xb);
+          if (gi + 1 < ngroups) do_group(gi + 1, xb, xa);
         }
-        quant_sync();                                  // every thread is done with this op's input amax
-        if (e < 16) amax_s[e] = 0;                     // from here on: running max of |y| for the next op
-        fence_proxy_async_smem();
-        quant_sync();
-        if (lane == 0) mbar_arrive(bready_bar);
         TC_TRACE(2);
 
         if (epi) {
