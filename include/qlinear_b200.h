@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define QL_ABI_VERSION 8
+#define QL_ABI_VERSION 9
 
 /* status codes */
 #define QL_OK 0
@@ -47,6 +47,7 @@ extern "C" {
 #define QL_ERR_WORKSPACE 5        /* caller-provided workspace too small or NULL */
 #define QL_ERR_CUDA 6             /* a CUDA runtime/driver call failed (launch error, TMA descriptor encode) */
 #define QL_ERR_NULL 7             /* required pointer is NULL */
+#define QL_ERR_STATIC_SCRATCH 8   /* ql_linear_static: the problem needs more than QL_STATIC_SCRATCH_BYTES of scratch */
 
 /* element formats of the quantized tensors */
 #define QL_INT8 0     /* torch.int8,          qmax 127 */
@@ -292,6 +293,42 @@ QL_API int ql_tp_allreduce_bf16(int64_t M, int64_t N, int pushed, void* out, int
 
 /* Bytes of caller-provided scratch ql_linear needs for an [M, K] activation (0 for M <= 16). */
 QL_API size_t ql_workspace_bytes(int64_t M, int64_t K);
+
+/*
+ * ql_linear without a workspace argument, for callers that cannot allocate one.
+ * (No counterpart in the reference: there every forward allocates through torch,
+ * nanovllm/utils/quantization.py:320-329.  This entry point exists for users of the C ABI.)
+ *
+ * Who needs it: a client that binds this library from C, ctypes or another FFI without torch has
+ * no caching allocator, only cudaMalloc -- and once the serving engine has given all remaining
+ * HBM to its KV cache, cudaMalloc fails, or at best stalls every stream of the device while it
+ * runs.  ql_linear_static therefore takes the same inputs and outputs as ql_linear and keeps the
+ * quantised activations (qx [M,K], sx [M]) in an array that is part of the library image:
+ * QL_STATIC_SCRATCH_BYTES (8 MiB) of device memory on EVERY GPU that loads the library, held
+ * until the process exits.  It calls no cudaMalloc / cudaFree and no allocating library routine.
+ *
+ * Limit: ql_workspace_bytes(M, K) <= QL_STATIC_SCRATCH_BYTES (also returned by
+ * ql_static_scratch_bytes()), e.g. 4096 tokens at K = 1024 or 2048 tokens at K = 3072.  Anything
+ * larger is refused with QL_ERR_STATIC_SCRATCH and nothing is launched -- split the tokens into
+ * several calls, or use ql_linear with your own workspace.
+ *
+ * Results are those of ql_linear on the same arguments, bit for bit (same kernels, same dispatch).
+ *
+ * Rules that come with a shared, never-freed scratch:
+ *   - the first call on each device looks the array's device address up (cudaGetSymbolAddress,
+ *     with that device current) and caches it; make that first call before any stream capture;
+ *   - all calls on a device use the same array.  Calls issued to ONE stream are safe back to
+ *     back; calls that can overlap on the GPU (different streams, or several host threads
+ *     feeding different streams) race on it and corrupt each other's activations -- order
+ *     them with events or use ql_linear with separate workspaces;
+ *   - the array keeps the previous call's bytes.  Nothing in it has to be zero: every call
+ *     rewrites all of qx and sx it later reads, so no clearing happens and none is needed.
+ */
+#define QL_STATIC_SCRATCH_BYTES (8u << 20)
+QL_API size_t ql_static_scratch_bytes(void);
+QL_API int ql_linear_static(const void* x, int64_t ldx, const void* qw, const float* sw,
+                     const void* bias, void* y, int64_t ldy, int64_t M, int64_t N, int64_t K,
+                     int fmt, int64_t group, ql_stream_t stream);
 
 /*
  * Decode-regime CHAIN of quantized linears in one persistent launch (csrc/decode_chain.cu).

@@ -18,7 +18,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT_DIR = os.path.join(HERE, "nanovllm", "_lib")
 OUT = os.path.join(OUT_DIR, "libqlinear_b200.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["api.cu", "quant.cu", "producers.cu", "allreduce.cu", "tp_collective.cu", "gemv.cu", "gemm_tcgen05.cu", "gemm_2cta.cu", "gemm_skinny.cu", "decode_chain.cu"]
+SOURCES = ["api.cu", "quant.cu", "producers.cu", "allreduce.cu", "tp_collective.cu", "gemv.cu", "gemm_tcgen05.cu", "gemm_2cta.cu", "gemm_skinny.cu", "decode_chain.cu", "static_scratch.cu"]
 HEADERS = ["common.cuh", "kernels.h", os.path.join("..", "..", "include", "qlinear_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

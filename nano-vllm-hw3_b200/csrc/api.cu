@@ -89,6 +89,9 @@ const char* ql_status_string(int status) {
     case QL_ERR_WORKSPACE: return "workspace missing or too small";
     case QL_ERR_CUDA: return "CUDA runtime/driver call failed";
     case QL_ERR_NULL: return "required pointer is NULL";
+    case QL_ERR_STATIC_SCRATCH:
+      return "problem too large for the library's built-in scratch (ql_workspace_bytes(M, K) > ql_static_scratch_bytes()); "
+             "split the tokens or call ql_linear with a workspace";
     default: return "unknown status";
   }
 }

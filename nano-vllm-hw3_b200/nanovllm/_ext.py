@@ -19,7 +19,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libqlinear_b200.so")
 
 QL_INT8, QL_FP8_E4M3 = 0, 1
-QL_ABI_VERSION = 8
+QL_ABI_VERSION = 9
 _FMT = {torch.int8: QL_INT8, torch.float8_e4m3fn: QL_FP8_E4M3}
 
 _c_i64, _c_int, _c_vp, _c_sz = ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
@@ -64,6 +64,9 @@ SIGNATURES = {
     "ql_tp_reduce_quant_gather": (_c_int, [_c_i64, _c_i64, _c_int, _c_int, _c_int, _c_vp]),
     "ql_tp_allreduce_bf16": (_c_int, [_c_i64, _c_i64, _c_int, _c_vp, _c_i64, _c_int, _c_vp]),
     "ql_workspace_bytes": (_c_sz, [_c_i64, _c_i64]),
+    "ql_static_scratch_bytes": (_c_sz, []),
+    "ql_linear_static": (_c_int, [_c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_i64, _c_i64,
+                                  _c_i64, _c_int, _c_i64, _c_vp]),
     "ql_chain_workspace_bytes": (_c_sz, [_c_vp, _c_int, _c_i64]),
     "ql_chain_prepare": (_c_int, [_c_vp, _c_int, _c_i64, _c_int, _c_i64, _c_vp, _c_sz, _c_vp, _c_vp]),
     "ql_chain_run": (_c_int, [_c_vp, _c_vp, _c_vp]),
