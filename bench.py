@@ -262,6 +262,8 @@ class LinearStack:
         want = os.environ.get("QL_TP_MICRO", "1")
         if self.tp == 1 or want != "2" or self.layers[0][1].group_size:
             return 1
+        if os.environ.get("QL_TP_ALLOW_CONCURRENT", "")[:1] != "1":
+            return 1     # the library refuses two channels without this second, explicit opt-in
         from nanovllm import _comm
         comm = _comm.get()
         if comm is None or comm.channels < 2 or T < 2 * 256 * self.tp:

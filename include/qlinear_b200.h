@@ -47,6 +47,7 @@ extern "C" {
 #define QL_ERR_WORKSPACE 5        /* caller-provided workspace too small or NULL */
 #define QL_ERR_CUDA 6             /* a CUDA runtime/driver call failed (launch error, TMA descriptor encode) */
 #define QL_ERR_NULL 7             /* required pointer is NULL */
+#define QL_ERR_GUARDED 9          /* channel > 0 / ql_tp_set_concurrent(1) without QL_TP_ALLOW_CONCURRENT=1 (known hazard, see ql_tp_channels) */
 #define QL_ERR_STATIC_SCRATCH 8   /* ql_linear_static: the problem needs more than QL_STATIC_SCRATCH_BYTES of scratch */
 
 /* element formats of the quantized tensors */
@@ -279,6 +280,14 @@ QL_API size_t ql_tp_max_hidden(void);
  *     next kernel only after their last cross-GPU wait: a GEMM parked behind a reduce kernel that
  *     waits for a peer would otherwise hold the shared memory the other channel's GEMM -- the one
  *     the peer is waiting for -- needs.  Call it before capturing CUDA graphs of channel 0.
+ *
+ * KNOWN HAZARD -- two channels in flight at once can hang.  One TP=8 run ended in the reduce
+ * kernel's bounded-wait trap (profiles/r2n_n8_ag_push_micro2_trap.err).  Only the reduce kernel's
+ * GRID is capped at one CTA per SM; the scheduler may still stack its spinning CTAs on one SM, the
+ * other channel's persistent GEMM CTA then has no SM to run its statically assigned tiles on, and
+ * the peer waits for those tiles: a cross-GPU cycle.  Until this is fixed, every call with
+ * channel > 0 and ql_tp_set_concurrent(1) return QL_ERR_GUARDED unless the environment variable
+ * QL_TP_ALLOW_CONCURRENT=1 is set (read at each call).  Channel 0 alone is unaffected.
  */
 QL_API int ql_tp_channels(void);
 QL_API int ql_tp_set_concurrent(int on);

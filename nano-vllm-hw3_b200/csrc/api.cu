@@ -92,6 +92,9 @@ const char* ql_status_string(int status) {
     case QL_ERR_STATIC_SCRATCH:
       return "problem too large for the library's built-in scratch (ql_workspace_bytes(M, K) > ql_static_scratch_bytes()); "
              "split the tokens or call ql_linear with a workspace";
+    case QL_ERR_GUARDED:
+      return "two-channel tensor-parallel mode is disabled: it has a known cross-GPU ordering hazard (can hang at TP=8); "
+             "set QL_TP_ALLOW_CONCURRENT=1 to opt in";
     default: return "unknown status";
   }
 }

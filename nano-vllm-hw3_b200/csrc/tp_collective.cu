@@ -411,7 +411,19 @@ size_t ql_tp_max_hidden(void) {
 
 int ql_tp_channels(void) { return kTpChannels; }
 
+// Two channels in flight at once have a KNOWN cross-GPU ordering hazard (bounded-wait trap at TP=8,
+// profiles/r2n_n8_ag_push_micro2_trap.err): only the GRID of tp_reduce_kernel is capped at one CTA
+// per SM, the hardware scheduler may still stack several of its spinning CTAs on one SM, where a
+// persistent, statically strided GEMM CTA of the other channel then cannot be placed -- and the peer
+// spins on the rows that GEMM would have pushed.  Until that is fixed the mode is refused unless the
+// caller opts in explicitly.
+static bool tp_concurrent_opt_in() {
+  const char* e = getenv("QL_TP_ALLOW_CONCURRENT");
+  return e != nullptr && e[0] == '1';
+}
+
 int ql_tp_set_concurrent(int on) {
+  if (on && !tp_concurrent_opt_in()) return QL_ERR_GUARDED;
   __atomic_store_n(&g_tp_concurrent, on ? 1 : 0, __ATOMIC_RELAXED);
   return QL_OK;
 }
@@ -431,6 +443,7 @@ void* ql_tp_buffer(int which, int channel) {
 int ql_tp_reduce_quant_gather(int64_t M, int64_t N, int fmt, int pushed, int channel, ql_stream_t stream) {
   if (fmt != QL_INT8 && fmt != QL_FP8_E4M3) return QL_ERR_BAD_FORMAT;
   if (channel < 0 || channel >= kTpChannels) return QL_ERR_BAD_SHAPE;
+  if (channel > 0 && !tp_concurrent_opt_in()) return QL_ERR_GUARDED;
   if (channel > 0) __atomic_store_n(&g_tp_concurrent, 1, __ATOMIC_RELAXED);
   TpView tp;
   if (!tp_view(&tp, channel)) return QL_ERR_WORKSPACE;
@@ -442,6 +455,7 @@ int ql_tp_reduce_quant_gather(int64_t M, int64_t N, int fmt, int pushed, int cha
 int ql_tp_allreduce_bf16(int64_t M, int64_t N, int pushed, void* out, int64_t ldo, int channel,
                          ql_stream_t stream) {
   if (channel < 0 || channel >= kTpChannels) return QL_ERR_BAD_SHAPE;
+  if (channel > 0 && !tp_concurrent_opt_in()) return QL_ERR_GUARDED;
   if (channel > 0) __atomic_store_n(&g_tp_concurrent, 1, __ATOMIC_RELAXED);
   TpView tp;
   if (!tp_view(&tp, channel)) return QL_ERR_WORKSPACE;
@@ -458,6 +472,7 @@ int ql_tp_gemm_push(const void* qx, const float* sx, const void* qw, const float
   if (fmt != QL_INT8 && fmt != QL_FP8_E4M3) return QL_ERR_BAD_FORMAT;
   if (M < 0 || N <= 0 || K <= 0 || K % 128 != 0) return QL_ERR_BAD_SHAPE;
   if (channel < 0 || channel >= kTpChannels) return QL_ERR_BAD_SHAPE;
+  if (channel > 0 && !tp_concurrent_opt_in()) return QL_ERR_GUARDED;
   if (channel > 0) __atomic_store_n(&g_tp_concurrent, 1, __ATOMIC_RELAXED);
   TpView tp;
   if (!tp_view(&tp, channel)) return QL_ERR_WORKSPACE;

@@ -23,7 +23,9 @@ refused, out of memory, different sizes per rank) every rank frees what it mappe
 The prefill-sized path has ``ql_tp_channels()`` independent channels (own buffers, flags, call
 counters).  A caller that splits a batch into token micro-batches and runs them on separate CUDA
 streams, one channel each (``nanovllm.layers.linear.tp_channel``), keeps one collective per channel
-in flight, so the wire time of one micro-batch hides under the GEMMs of the other.
+in flight, so the wire time of one micro-batch hides under the GEMMs of the other.  That mode has a
+KNOWN HANG HAZARD at TP=8 (include/qlinear_b200.h, ql_tp_channels): every call on a channel > 0 is
+refused (status 9 -> RuntimeError) unless ``QL_TP_ALLOW_CONCURRENT=1`` is set.
 """
 from __future__ import annotations
 

@@ -18,6 +18,7 @@ bias on rank 0 only and all-reduces the bf16 partial sums, as linear.py:150-152)
 from __future__ import annotations
 
 import contextlib
+import os
 
 import torch
 import torch.distributed as dist
@@ -35,9 +36,18 @@ def tp_channel(channel: int):
     """Route the prefill-sized NVLink collectives of the row-parallel linears called inside the
     block through ``channel`` (0 .. ql_tp_channels()-1; independent buffers, flags and call counters,
     include/qlinear_b200.h).  A caller that runs two token micro-batches on two CUDA streams gives
-    each its own channel; every rank must use the same channel for the same micro-batch."""
+    each its own channel; every rank must use the same channel for the same micro-batch.
+
+    KNOWN HAZARD: two channels in flight at once can hang at TP=8 (a cross-GPU placement cycle
+    between one channel's spinning reduce CTAs and the other's persistent GEMM; see
+    include/qlinear_b200.h, ql_tp_channels).  The mode is therefore refused -- RuntimeError --
+    unless ``QL_TP_ALLOW_CONCURRENT=1`` is set in the environment."""
+    if os.environ.get("QL_TP_ALLOW_CONCURRENT", "")[:1] != "1":
+        raise RuntimeError(
+            "tp_channel: the two-channel tensor-parallel pipeline has a known cross-GPU ordering hazard "
+            "(can hang at TP=8); set QL_TP_ALLOW_CONCURRENT=1 to opt in")
     prev = _tp_channel[0]
-    _ext.load().ql_tp_set_concurrent(1)   # reduce kernels release their stream late from here on
+    _ext._check(_ext.load().ql_tp_set_concurrent(1))   # reduce kernels release their stream late from here on
     _tp_channel[0] = int(channel)
     try:
         yield

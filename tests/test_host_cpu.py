@@ -100,6 +100,26 @@ def test_validation_precedes_device_work(lib):
     assert lib.ql_linear(fake, 128, fake, fake, None, fake, 8, 0, 8, 128, 0, 0, None, 0, None) == 0
 
 
+def test_two_channel_tp_mode_needs_an_explicit_opt_in(lib, monkeypatch):
+    """the two-channel pipeline can hang at TP=8; it is refused unless opted into."""
+    from nanovllm.layers import linear as L
+    monkeypatch.delenv("QL_TP_ALLOW_CONCURRENT", raising=False)
+    assert lib.ql_tp_set_concurrent(1) == 9
+    assert lib.ql_tp_reduce_quant_gather(512, 1024, 0, 0, 1, None) == 9
+    assert lib.ql_tp_gemm_push(None, None, None, None, None, 512, 1024, 1024, 0, 1, None) == 9
+    assert "QL_TP_ALLOW_CONCURRENT" in lib.ql_status_string(9).decode()
+    with pytest.raises(RuntimeError, match="QL_TP_ALLOW_CONCURRENT"):
+        with L.tp_channel(1):
+            pass
+    assert lib.ql_tp_set_concurrent(0) == 0
+    monkeypatch.setenv("QL_TP_ALLOW_CONCURRENT", "1")
+    assert lib.ql_tp_set_concurrent(1) == 0
+    with L.tp_channel(1):
+        assert L._tp_channel[0] == 1
+    assert L._tp_channel[0] == 0
+    assert lib.ql_tp_set_concurrent(0) == 0
+
+
 @pytest.mark.skipif(torch.cuda.is_available(), reason="CPU-box behaviour")
 def test_no_cpu_fallback(lib):
     from nanovllm import _ext

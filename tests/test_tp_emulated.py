@@ -13,6 +13,7 @@ for every rank's copy of the gathered codes / scales / bf16 rows; partial_r = th
 row-parallel GEMM output (checked through the PUSH kernel against ql_gemm_w8a8 on the same operands).
 """
 import ctypes
+import os
 
 import numpy as np
 import pytest
@@ -38,6 +39,9 @@ class Emu:
     def __init__(self, ext, world):
         self.ext, self.lib, self.world = ext, ext.load(), world
         self.ch = 1 if world == 4 else 0          # the channels are independent copies: cover both
+        # channel 1 needs the explicit opt-in (the hazard is two channels IN FLIGHT AT ONCE; these
+        # tests use one channel at a time on one stream, which is safe)
+        os.environ["QL_TP_ALLOW_CONCURRENT"] = "1" if self.ch else "0"
         self.lib.ql_ar_destroy()
         ext._check(self.lib.ql_ar_init_local(1 << 16, TOKENS, HIDDEN, world))
 
@@ -214,4 +218,15 @@ def test_capacity_and_argument_checks(ext, emu):
     assert lib.ql_tp_reduce_quant_gather(0, 1024, 0, 0, 0, None) == 0               # empty: nothing to do
     assert lib.ql_tp_emu_set_rank(emu.world) == 2
     assert lib.ql_tp_reduce_quant_gather(512, 1024, 0, 0, lib.ql_tp_channels(), None) == 2   # no such channel
+    # channel 1 without the opt-in: refused with the hazard's own status, before any launch
+    saved = os.environ.get("QL_TP_ALLOW_CONCURRENT")
+    os.environ["QL_TP_ALLOW_CONCURRENT"] = "0"
+    try:
+        before = lib.ql_launch_count()
+        assert lib.ql_tp_reduce_quant_gather(512, 1024, 0, 0, 1, None) == 9
+        assert lib.ql_tp_allreduce_bf16(512, 1024, 0, ctypes.c_void_p(16), 1024, 1, None) == 9
+        assert lib.ql_tp_set_concurrent(1) == 9
+        assert lib.ql_launch_count() == before
+    finally:
+        os.environ["QL_TP_ALLOW_CONCURRENT"] = saved if saved is not None else "0"
     assert lib.ql_ar_allreduce_bf16(ctypes.c_void_p(16), ctypes.c_void_p(16), 8, None) == 5   # one-shot path is not emulated
