@@ -288,6 +288,12 @@ QL_API size_t ql_tp_max_hidden(void);
  * the peer waits for those tiles: a cross-GPU cycle.  Until this is fixed, every call with
  * channel > 0 and ql_tp_set_concurrent(1) return QL_ERR_GUARDED unless the environment variable
  * QL_TP_ALLOW_CONCURRENT=1 is set (read at each call).  Channel 0 alone is unaffected.
+ *
+ *   ql_tp_channels(): channels the symmetric area holds -- 1 by default; 2 only when
+ *     QL_TP_ALLOW_CONCURRENT=1 was set when ql_ar_init / ql_ar_init_local ran (channel 1's buffers
+ *     are as large as channel 0's, ~1.4 GB at 65536 tokens x 4096, and would otherwise come out of
+ *     the KV-cache budget for nothing).  A channel that was not allocated gets QL_ERR_WORKSPACE.
+ *     Every rank must run with the same setting.
  */
 QL_API int ql_tp_channels(void);
 QL_API int ql_tp_set_concurrent(int on);

@@ -38,6 +38,7 @@ struct ArState {
   int world = 0, rank = 0;
   size_t bytes = 0;                         // largest payload (bf16 bytes) of one one-shot call
   size_t big_rows = 0, big_hidden = 0;      // capacity of the large (reduce-scatter) path, 0 = off
+  int channels = 0;                         // big sections allocated: 1, or 2 with QL_TP_ALLOW_CONCURRENT=1 at init
   uint8_t* local = nullptr;                 // this rank's receive area + counters
   uint8_t* peer[kArMaxWorld] = {};          // everybody's area as mapped here (peer[rank] == local)
 };
@@ -60,22 +61,29 @@ static void big_layout(size_t rows, size_t hidden, int world, TpLayout* L) {
   L->y = L->s + rup(cap * 4, 1024);
   L->total = L->y + rup(cap * hidden * 2, 1024);
 }
-static size_t ar_alloc_bytes(size_t bytes, int world, size_t rows, size_t hidden) {
+// Channel 1 only serves the opt-in two-channel pipeline (tp_collective.cu): its section -- as large
+// as channel 0's, ~1.4 GB at the default 65536 x 4096 capacity -- is allocated only when the opt-in
+// is set at init time.  Channel 0's offsets do not depend on the count.
+static int ar_want_channels() {
+  const char* e = getenv("QL_TP_ALLOW_CONCURRENT");
+  return (e != nullptr && e[0] == '1') ? kTpChannels : 1;
+}
+static size_t ar_alloc_bytes(size_t bytes, int world, size_t rows, size_t hidden, int channels) {
   size_t total = ar_big_offset(bytes, world);
   if (rows > 0 && hidden > 0) {
     TpLayout L;
     big_layout(rows, hidden, world, &L);
-    total += kTpChannels * rup(L.total, 4096);
+    total += (size_t)channels * rup(L.total, 4096);
   }
   return total;
 }
 
 // flags and call counters of every channel start at epoch 0
-static bool big_clear_flags(uint8_t* area, size_t bytes, int world, size_t rows, size_t hidden) {
+static bool big_clear_flags(uint8_t* area, size_t bytes, int world, size_t rows, size_t hidden, int channels) {
   if (rows == 0 || hidden == 0) return true;
   TpLayout L;
   big_layout(rows, hidden, world, &L);
-  for (int c = 0; c < kTpChannels; ++c)
+  for (int c = 0; c < channels; ++c)
     if (cudaMemset(area + ar_big_offset(bytes, world) + (size_t)c * rup(L.total, 4096) + L.flags, 0, 4096) !=
         cudaSuccess)
       return false;
@@ -192,7 +200,7 @@ bool ar_view(ArView* v) {
 }
 
 bool tp_view(TpView* v, int channel) {
-  if (!g_ar.ready || g_ar.big_rows == 0 || channel < 0 || channel >= kTpChannels) return false;
+  if (!g_ar.ready || g_ar.big_rows == 0 || channel < 0 || channel >= g_ar.channels) return false;
   big_layout(g_ar.big_rows, g_ar.big_hidden, g_ar.world, &v->lay);
   const size_t off = ar_big_offset(g_ar.bytes, g_ar.world) + (size_t)channel * rup(v->lay.total, 4096);
   for (int r = 0; r < kArMaxWorld; ++r) v->big[r] = r < g_ar.world ? g_ar.peer[r] + off : nullptr;
@@ -205,6 +213,8 @@ bool tp_view(TpView* v, int channel) {
   v->timeout_ns = ar_timeout_ns();
   return true;
 }
+
+int tp_channels_allocated() { return (g_ar.ready && g_ar.big_rows != 0) ? g_ar.channels : ar_want_channels(); }
 
 }  // namespace ql
 
@@ -240,12 +250,13 @@ int ql_ar_init(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int world, 
   if (!handle_out) return QL_ERR_NULL;
   if (g_ar.local != nullptr) return QL_ERR_BAD_SHAPE;   // one communicator per process (one process per GPU)
   if (int e = ql_device_check()) return e;
-  const size_t total = ar_alloc_bytes(max_bytes, world, rs_tokens, rs_hidden);
+  const int channels = ar_want_channels();
+  const size_t total = ar_alloc_bytes(max_bytes, world, rs_tokens, rs_hidden, channels);
   uint8_t* ptr = nullptr;
   if (cudaMalloc(&ptr, total) != cudaSuccess) { (void)cudaGetLastError(); return QL_ERR_CUDA; }
   // only the packet regions, counters and flags need a defined initial state (epoch 0)
   const size_t head = ar_big_offset(max_bytes, world);
-  if (cudaMemset(ptr, 0, head) != cudaSuccess || !big_clear_flags(ptr, max_bytes, world, rs_tokens, rs_hidden) ||
+  if (cudaMemset(ptr, 0, head) != cudaSuccess || !big_clear_flags(ptr, max_bytes, world, rs_tokens, rs_hidden, channels) ||
       cudaDeviceSynchronize() != cudaSuccess) {
     (void)cudaGetLastError();
     cudaFree(ptr);
@@ -262,6 +273,7 @@ int ql_ar_init(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int world, 
   g_ar.bytes = max_bytes;
   g_ar.big_rows = rs_tokens;
   g_ar.big_hidden = rs_hidden;
+  g_ar.channels = channels;
   g_ar.world = world;
   g_ar.rank = rank;
   return QL_OK;
@@ -296,12 +308,13 @@ int ql_ar_init_local(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int w
     return QL_ERR_BAD_SHAPE;
   if (g_ar.local != nullptr) return QL_ERR_BAD_SHAPE;
   if (int e = ql_device_check()) return e;
-  const size_t total = ar_alloc_bytes(max_bytes, world, rs_tokens, rs_hidden);
+  const int channels = ar_want_channels();
+  const size_t total = ar_alloc_bytes(max_bytes, world, rs_tokens, rs_hidden, channels);
   const size_t head = ar_big_offset(max_bytes, world);
   for (int r = 0; r < world; ++r) {
     uint8_t* ptr = nullptr;
     if (cudaMalloc(&ptr, total) != cudaSuccess || cudaMemset(ptr, 0, head) != cudaSuccess ||
-        !big_clear_flags(ptr, max_bytes, world, rs_tokens, rs_hidden)) {
+        !big_clear_flags(ptr, max_bytes, world, rs_tokens, rs_hidden, channels)) {
       (void)cudaGetLastError();
       if (ptr != nullptr) cudaFree(ptr);
       for (int k = 0; k < r; ++k) { cudaFree(g_ar.peer[k]); g_ar.peer[k] = nullptr; }
@@ -314,6 +327,7 @@ int ql_ar_init_local(size_t max_bytes, size_t rs_tokens, size_t rs_hidden, int w
   g_ar.bytes = max_bytes;
   g_ar.big_rows = rs_tokens;
   g_ar.big_hidden = rs_hidden;
+  g_ar.channels = channels;
   g_ar.world = world;
   g_ar.rank = 0;
   g_ar.emulated = true;

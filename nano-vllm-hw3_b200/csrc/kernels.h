@@ -86,6 +86,9 @@ struct TpView {
 // under the GEMMs of the other.
 constexpr int kTpChannels = 2;
 bool tp_view(TpView* v, int channel = 0);
+// big sections in the current area (1, or kTpChannels when QL_TP_ALLOW_CONCURRENT=1 was set at init);
+// before init: what an init would allocate now
+int tp_channels_allocated();
 constexpr size_t kTpReadyOff = 0, kTpDoneOff = 1024, kTpCtrOff = 2048, kTpFlagStride = 128;
 // rows per token owner: whole 256-token pair tiles, so that a GEMM tile never straddles two owners
 inline int64_t tp_rows_per_owner(int64_t M, int world) {

@@ -409,7 +409,7 @@ size_t ql_tp_max_hidden(void) {
   return tp_view(&tp) ? tp.hidden : 0;
 }
 
-int ql_tp_channels(void) { return kTpChannels; }
+int ql_tp_channels(void) { return tp_channels_allocated(); }
 
 // Two channels in flight at once have a KNOWN cross-GPU ordering hazard (bounded-wait trap at TP=8,
 // profiles/r2n_n8_ag_push_micro2_trap.err): only the GRID of tp_reduce_kernel is capped at one CTA

@@ -79,7 +79,7 @@ class PeerAllReduce:
         world, rank = dist.get_world_size(), dist.get_rank()
         # every rank must ask for the same area, or remote offsets would be wrong
         sizes = [None] * world
-        dist.all_gather_object(sizes, (max_bytes, tp_tokens, tp_hidden))
+        dist.all_gather_object(sizes, (max_bytes, tp_tokens, tp_hidden, int(lib.ql_tp_channels())))
         if len(set(sizes)) != 1:
             return None
         if not _all_ok(lib.ql_ar_can_access_peers(world) == 0):
@@ -185,6 +185,20 @@ class PeerAllReduce:
         return out
 
 
+def configure(max_tokens: int | None = None, hidden: int | None = None) -> None:
+    """Size the prefill-sized path for the model instead of the generic default (65536 tokens x
+    4096 hidden, ~1.4 GB per channel): pass the engine's ``max_num_batched_tokens`` and the model's
+    ``hidden_size`` BEFORE the first tensor-parallel forward, identically on every rank.  The memory
+    comes out of what the KV cache could otherwise use.  ``QL_TP_TOKENS`` / ``QL_TP_HIDDEN`` in the
+    environment still win.  Has no effect once the communicator exists."""
+    if max_tokens is not None:
+        assert max_tokens > 0
+        _state["tokens"] = int(max_tokens)
+    if hidden is not None:
+        assert hidden > 0 and hidden % 8 == 0
+        _state["hidden"] = int(hidden)
+
+
 def get() -> PeerAllReduce | None:
     """The process-wide communicator, created on first use (never during CUDA-graph capture:
     callers run one eager forward first, as the engine's warm-up does, model_runner.py:91-103).
@@ -201,8 +215,8 @@ def get() -> PeerAllReduce | None:
     if dist.get_backend() != "nccl" or dist.get_world_size() not in (2, 4, 8):
         return None
     big = os.environ.get("QL_TP_BIG", "1") != "0"
-    tokens = int(os.environ.get("QL_TP_TOKENS", str(65536))) if big else 0
-    hidden = int(os.environ.get("QL_TP_HIDDEN", str(4096))) if big else 0
+    tokens = int(os.environ.get("QL_TP_TOKENS", str(_state.get("tokens", 65536)))) if big else 0
+    hidden = int(os.environ.get("QL_TP_HIDDEN", str(_state.get("hidden", 4096)))) if big else 0
     try:
         _state["comm"] = PeerAllReduce.create(int(os.environ.get("QL_PEER_AR_BYTES", str(1 << 20))),
                                               tokens, hidden)

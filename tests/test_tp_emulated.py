@@ -217,7 +217,8 @@ def test_capacity_and_argument_checks(ext, emu):
     assert lib.ql_tp_reduce_quant_gather(512, 1024, 9, 0, 0, None) == 1             # bad format
     assert lib.ql_tp_reduce_quant_gather(0, 1024, 0, 0, 0, None) == 0               # empty: nothing to do
     assert lib.ql_tp_emu_set_rank(emu.world) == 2
-    assert lib.ql_tp_reduce_quant_gather(512, 1024, 0, 0, lib.ql_tp_channels(), None) == 2   # no such channel
+    assert lib.ql_tp_reduce_quant_gather(512, 1024, 0, 0, 2, None) == 2   # no such channel, whatever was allocated
+    assert lib.ql_tp_channels() == (2 if emu.ch else 1)                # channel 1 exists only with the opt-in at init
     # channel 1 without the opt-in: refused with the hazard's own status, before any launch
     saved = os.environ.get("QL_TP_ALLOW_CONCURRENT")
     os.environ["QL_TP_ALLOW_CONCURRENT"] = "0"
