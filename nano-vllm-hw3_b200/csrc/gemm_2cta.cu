@@ -434,13 +434,15 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tm_x, const CUtens
       if (lane == 0) mbar_arrive_cluster(tempty_leader0 + acc * 8);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-    // PUSH: the CTA only waits until the store engine has READ its staging tiles, not for the
-    // peers' write acknowledgements (a NVLink round trip): the grid does not complete before its
-    // bulk stores have, and the reduce kernel behind it in the stream signals the peers -- the SM
-    // is free for the other channel's GEMM meanwhile.
-    if (lane == 0) {
-      if constexpr (PUSH) tma_store_wait_read<0>(); else tma_store_wait_all();
-    }
+    // Every bulk store of this CTA must be COMPLETE (written, not merely read out of the staging
+    // tiles) before the CTA exits.  For PUSH the destinations are peer memory and the reduce kernel
+    // behind this one in the stream tells the peers "your rows have landed" with an st.release.sys
+    // flag: that is only true if the async-proxy stores were performed first.  Grid completion is
+    // widely assumed to imply it, but nothing we can cite says so for cp.async.bulk groups that
+    // were never waited on, and a violation would show up as rare stale rows -- so the last thing
+    // the epilogue does is wait for the whole group (one NVLink round trip per CTA, paid while the
+    // dependent reduce kernel is still parked at its griddepcontrol.wait anyway).
+    if (lane == 0) tma_store_wait_all();
     if (threadIdx.x == 128) G2_TRACE(6);
   }
 

@@ -157,6 +157,62 @@ def test_push_gemm_reduce_quant_gather(ext, emu, ag_mode, dn, bias, M, N, K):
         assert torch.equal(emu.buf(r, 1, M * N), q.view(torch.uint8).view(-1)), r
 
 
+def _push_round(ext, emu, dtype, M, N, K, seed, bias=False):
+    """One row-parallel linear on every emulated rank (inputs made on the GPU: the 8B shards are
+    large) -> the un-fused kernel's partials, with the pushed copies sitting in the owners' areas."""
+    W = emu.world
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    parts = []
+    for r in range(W):
+        x = torch.randn(M, K, generator=g, device="cuda").to(torch.bfloat16)
+        w = (torch.randn(N, K, generator=g, device="cuda") * 0.02).to(torch.bfloat16)
+        b = torch.randn(N, generator=g, device="cuda").to(torch.bfloat16) if (bias and r == 0) else None
+        qx, sx = ext.quant_rows(x, dtype)
+        qw, sw = ext.quant_rows(w, dtype)
+        parts.append(ext.gemm_w8a8(qx, sx, qw, sw, b, dtype))
+        ext._check(emu.lib.ql_tp_emu_set_rank(r))
+        ext._check(emu.lib.ql_tp_gemm_push(qx.data_ptr(), sx.data_ptr(), qw.data_ptr(), sw.data_ptr(),
+                                           None if b is None else b.data_ptr(), M, N, K, ext.fmt_of(dtype),
+                                           emu.ch, emu.stream()))
+    return parts
+
+
+@pytest.mark.parametrize("dn", ["i8", "f8"])
+@pytest.mark.parametrize("K", [512, 1536, 2048, 6144])
+def test_push_gemm_qwen3_8b_shards(ext, emu, dn, K):
+    """BASELINE configs[3]: the row-parallel shards of Qwen3-8B (hidden 4096; o_proj K = 4096/tp,
+    down_proj K = 12288/tp: 512 and 1536 at TP=8, 2048 and 6144 at TP=2) through gemm2_push_kernel
+    + tp_reduce_kernel, against the un-fused GEMM + "fp32 rank-order sum -> bf16 -> ql_quant_rows"."""
+    W, dtype, M, N = emu.world, DT[dn], 1280, 4096
+    parts = _push_round(ext, emu, dtype, M, N, K, 8000 + K + W)
+    y, q, s = _expected(ext, parts, dtype)
+    ext._check(emu.lib.ql_tp_reduce_quant_gather(M, N, ext.fmt_of(dtype), 1, emu.ch, emu.stream()))
+    torch.cuda.synchronize()
+    for r in range(W):
+        assert torch.equal(emu.buf(r, 2, M * 4).view(torch.float32), s), r
+        assert torch.equal(emu.buf(r, 1, M * N), q.view(torch.uint8).view(-1)), r
+
+
+def test_push_into_poisoned_receive_regions(ext, emu):
+    """the reduce kernel may only read rows the GEMM epilogue's bulk stores have
+    completed.  Every iteration pushes NEW data into receive regions (and result buffers) that were
+    overwritten with a poison pattern after the previous one; a stale or missing row cannot match."""
+    W, dtype, (M, N, K) = emu.world, torch.int8, (1024, 2048, 256)
+    cap = emu.lib.ql_tp_max_tokens() * emu.lib.ql_tp_max_hidden()
+    for it in range(12):
+        for r in range(W):
+            emu.buf(r, 0, cap * 2).fill_(0x7F)            # bf16 0x7f7f = NaN: poisons any sum it enters
+            emu.buf(r, 1, M * N).fill_(0x55)
+            emu.buf(r, 2, M * 4).view(torch.float32).fill_(-1.0)
+        parts = _push_round(ext, emu, dtype, M, N, K, 500 + 31 * it + W, bias=bool(it & 1))
+        ext._check(emu.lib.ql_tp_reduce_quant_gather(M, N, ext.fmt_of(dtype), 1, emu.ch, emu.stream()))
+        _, q, s = _expected(ext, parts, dtype)
+        torch.cuda.synchronize()
+        for r in range(W):
+            assert torch.equal(emu.buf(r, 2, M * 4).view(torch.float32), s), (it, r)
+            assert torch.equal(emu.buf(r, 1, M * N), q.view(torch.uint8).view(-1)), (it, r)
+
+
 def test_push_allreduce_bf16_and_graph_replay(ext, emu):
     """The bf16 form after pushed partials, captured in a CUDA graph and replayed (the engine
     captures its steps, model_runner.py:316-356): the device-side call counters keep every
