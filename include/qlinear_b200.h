@@ -365,7 +365,11 @@ QL_API int ql_linear_static(const void* x, int64_t ldx, const void* qw, const fl
  *     any of them changes;
  *   ql_chain_run: ONE kernel launch (cooperative + cluster launch, one CTA per SM, all
  *     co-resident; every CTA spins on a bounded grid barrier between ops); capturable into a CUDA
- *     graph.  Runs of one workspace must not overlap each other.
+ *     graph.  Runs of one workspace must not overlap each other.  If the driver refuses the
+ *     cooperative launch the call fails with QL_ERR_CUDA and launches nothing: without the
+ *     residency guarantee another stream holding SMs would make the grid barrier spin into its
+ *     bounded-wait trap.  QL_CHAIN_ALLOW_NONCOOP=1 falls back to a plain cluster launch instead
+ *     (only for a caller that keeps the device otherwise idle).
  * Measured on B200: correct but SLOWER than one ql_linear per op (a
  * dependent op costs ~5 us of release / barrier / activation round trips either way); kept as an
  * experiment that bench.py reports next to the per-linear launches.

@@ -1160,23 +1160,22 @@ int ql_chain_run(const ql_chain_plan* plan, void* workspace, ql_stream_t stream)
   // every CTA spins on the grid barrier: the grid must be co-resident.  Cooperative launch makes the
   // driver check that; where it refuses the cluster + cooperative combination the grid is still
   // sized by cudaOccupancyMaxActiveClusters (chain_max_clusters) and the barrier spin is bounded.
-  static int coop_ok = 1;
+  // A refused cooperative launch is an ERROR by default: a plain cluster launch has no residency
+  // guarantee, and if another stream holds SMs the grid barrier would spin until its bounded wait
+  // traps and poisons the context.  QL_CHAIN_ALLOW_NONCOOP=1 accepts that risk (a caller that
+  // knows the device is otherwise idle).
   cudaLaunchConfig_t cfg;
   cudaLaunchAttribute attr[2];
   void* args[] = {&p};
-  cudaError_t err = cudaErrorUnknown;
-  if (coop_ok) {
-    chain_launch_cfg(&cfg, attr, pl.clusters, 1, (cudaStream_t)stream, pl.tc);
-    err = cudaLaunchKernelExC(&cfg, kern, args);
-    if (err != cudaSuccess) {
-      if (getenv("QL_DEBUG") != nullptr)
-        fprintf(stderr, "[qlinear_b200] decode chain: cooperative cluster launch refused (%s), plain cluster launch\n",
-                cudaGetErrorString(err));
-      (void)cudaGetLastError();
-      coop_ok = 0;
-    }
-  }
-  if (!coop_ok) {
+  chain_launch_cfg(&cfg, attr, pl.clusters, 1, (cudaStream_t)stream, pl.tc);
+  cudaError_t err = cudaLaunchKernelExC(&cfg, kern, args);
+  if (err != cudaSuccess) {
+    const char* allow = getenv("QL_CHAIN_ALLOW_NONCOOP");
+    if (getenv("QL_DEBUG") != nullptr)
+      fprintf(stderr, "[qlinear_b200] decode chain: cooperative cluster launch refused (%s)%s\n",
+              cudaGetErrorString(err), (allow && allow[0] == '1') ? ", plain cluster launch" : "");
+    (void)cudaGetLastError();
+    if (allow == nullptr || allow[0] != '1') return QL_ERR_CUDA;
     chain_launch_cfg(&cfg, attr, pl.clusters, 0, (cudaStream_t)stream, pl.tc);
     err = cudaLaunchKernelExC(&cfg, kern, args);
   }

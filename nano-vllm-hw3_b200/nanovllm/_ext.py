@@ -218,14 +218,19 @@ def _prep_linear(x, qw, sw, bias, group_size):
 
 # One scratch buffer per (device, stream) instead of a torch.empty per call: every use is ordered
 # on that stream (the next call's quantiser starts behind griddepcontrol.wait, i.e. after the GEMM
-# that read the buffer has finished).  Buffers only grow and outgrown ones are kept alive, so a
-# pointer handed to a kernel never dangles.  During CUDA-graph capture the scratch comes from
-# the graph's own pool instead (graphs captured on one stream may be replayed concurrently).
-_WS, _WS_KEEP = {}, []
+# that read the buffer has finished; tests/test_gpu_parity.py::test_linear_shared_workspace_back_to_back
+# pins that).  A buffer is replaced only when a larger one is needed, and the old one is released
+# after its stream has drained, so a pointer handed to a kernel never dangles and nothing piles up.
+# During CUDA-graph capture the scratch comes from the graph's own pool instead (graphs captured on
+# one stream may be replayed concurrently).
+_WS = {}
+_get_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)     # private but cheap; public fallback below
 
 
 def _raw_stream(index: int) -> int:
-    return torch._C._cuda_getCurrentRawStream(index)
+    if _get_raw_stream is not None:
+        return _get_raw_stream(index)
+    return torch.cuda.current_stream(index).cuda_stream
 
 
 def _workspace(dev, index: int, stream: int, nbytes: int):
@@ -235,7 +240,11 @@ def _workspace(dev, index: int, stream: int, nbytes: int):
     ws = _WS.get(key)
     if ws is None or ws.numel() < nbytes:
         if ws is not None:
-            _WS_KEEP.append(ws)
+            # the kernels still reading the outgrown buffer are all on this stream: drain it, then
+            # let the caching allocator have the block back (growth is rare: sizes only go up)
+            torch.cuda.current_stream(index).synchronize()
+            del _WS[key]
+            ws = None
         ws = torch.empty((max(nbytes, 1 << 20),), dtype=torch.uint8, device=dev)
         _WS[key] = ws
     return ws

@@ -711,3 +711,44 @@ def test_linear_dispatch_and_cuda_graph(ext):
     torch.cuda.synchronize()
     assert torch.equal(out, up(xs))
     assert torch.equal(out.float() * 2, eager.float())
+
+
+# ------------------------------------------------------------------ shared workspace under PDL
+def test_linear_shared_workspace_back_to_back(ext):
+    """nanovllm._ext keeps ONE scratch buffer per (device, stream) and the kernels are
+    launched with programmatic dependent launch, so call i+1's quantiser may start while call i's
+    GEMM still reads the buffer -- it must not write before that GEMM is done.  Differently sized
+    linears (prefill tiles, ragged M, decode) are issued back to back with no synchronisation and
+    every output must carry the bits of the same call made alone with a private workspace."""
+    lib = ext.load()
+    shapes = [(4096, 1024, 1024), (17, 4096, 1024), (300, 1024, 3072), (2048, 2048, 2048), (16, 1024, 4096),
+              (1000, 6144, 1024), (64, 1024, 2048), (4096, 1024, 3072), (33, 512, 384), (129, 4096, 1024)]
+    for kind, group in (("i8", 0), ("f8", 0), ("i8", 128)):
+        dtype = DT[kind]
+        probs = []
+        for i, (M, N, K) in enumerate(shapes):
+            g = torch.Generator(device="cuda").manual_seed(1000 + i)
+            x = torch.randn(M, K, generator=g, device="cuda").to(torch.bfloat16)
+            w = (torch.randn(N, K, generator=g, device="cuda") * 0.02).to(torch.bfloat16)
+            qw, sw = ext.quant_groups(w, group, dtype) if group else ext.quant_rows(w, dtype)
+            probs.append((x, qw, sw))
+        # reference bits: each call alone, its own workspace, synchronised on both sides
+        refs = []
+        for x, qw, sw in probs:
+            M, K = x.shape
+            N = qw.shape[0]
+            y = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+            nbytes = lib.ql_workspace_bytes(M, K)
+            ws = torch.empty(max(nbytes, 16), dtype=torch.uint8, device="cuda")
+            torch.cuda.synchronize()
+            ext._check(lib.ql_linear(x.data_ptr(), K, qw.data_ptr(), sw.data_ptr(), None, y.data_ptr(), N, M, N, K,
+                                     ext.fmt_of(dtype), group, ws.data_ptr(), nbytes,
+                                     torch.cuda.current_stream().cuda_stream))
+            torch.cuda.synchronize()
+            refs.append(y)
+        for rep in range(3):
+            order = list(range(len(probs))) if rep == 0 else list(torch.randperm(len(probs)).tolist())
+            outs = {i: ext.linear(*probs[i], None, dtype, group) for i in order for _ in (0,)}
+            torch.cuda.synchronize()
+            for i in order:
+                assert torch.equal(outs[i], refs[i]), (kind, group, rep, shapes[i])
