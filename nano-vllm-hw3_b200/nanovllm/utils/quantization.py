@@ -1,7 +1,9 @@
 """Quantization ops and module wrappers -- the reference's nanovllm/utils/quantization.py
 surface, backed by the sm_100a library instead of Triton / eager torch.
 
-Same names, argument order and assertion behaviour as the reference:
+Same names, argument order and assertion behaviour as the reference (the holder classes QLinear /
+QTensorLinear / QGroupLinear are RESTATED from :349-401 -- they are the plugin boundary, SURVEY 8b --
+and everything they call is new):
 
     per_row_quant :147-163        per_row_matmul :310-346       QLinear :349-364
     per_group_quant :194-234      per_group_matmul :265-307     QGroupLinear :385-401
@@ -169,7 +171,14 @@ def apply_group_quant(model, dtype, group_size: int):
 
 
 def apply_quantization(model, linear_dtype, quant_type: str | None = None, group_size: int = 128):
-    """The dispatch of ModelRunner.__init__ (engine/model_runner.py:36-57) as one function."""
+    """The dispatch of ModelRunner.__init__ (engine/model_runner.py:36-57) as one function, for the
+    branches that are in scope: "per_tensor", "per_row", "per_group", and ``quant_type=None`` with a
+    non-bf16 ``linear_dtype`` (per-row, the reference's default rule).
+
+    Two branches differ from the reference ON PURPOSE: ``quant_type="smoothquant"`` goes to torchao
+    there (:43-46; third-party arithmetic no reference test pins, out of scope) and any
+    other unknown string is silently ignored there (:47-54 fall through).  Both raise ValueError
+    here: running a bf16 model when a quantised one was asked for is not a result worth hiding."""
     if quant_type is not None:
         if quant_type == "per_tensor":
             apply_tensor_quant(model, linear_dtype)
