@@ -346,6 +346,22 @@ def tp_check(stack, T, dtype, rank, world):
             ok = bool(torch.equal(y, y_def) and torch.equal(qa.s, s_def)
                       and torch.equal(qa.q.view(torch.uint8), q_def.view(torch.uint8)))
         info["checked"].append({"tokens": M, "hidden": N, "collective": which, "bit_identical": ok})
+        if ok and comm is not None and comm.fits_fused(M, N):
+            # the fused all-reduce + residual add + RMSNorm + quantiser (ar_rmsnorm_quant_kernel,
+            # RMSNorm.forward_quant(partial=True), layernorm.py:28-40 behind linear.py:150-152): its
+            # definition is ql_rmsnorm_quant on the rank-order-summed bf16 tensor
+            from nanovllm.layers.layernorm import RMSNorm
+            norm = RMSNorm(N).cuda()
+            gn = torch.Generator(device="cuda").manual_seed(7)                      # same on every rank
+            norm.weight.data = (1 + 0.1 * torch.randn(N, generator=gn, device="cuda")).to(torch.bfloat16)
+            res = torch.randn(M, N, generator=gn, device="cuda").to(torch.bfloat16)
+            qa2, res2 = norm.forward_quant(part, res, dtype, partial=True)
+            qd, sd, _, resd = norm._run(y_def, res, dtype, False)
+            torch.cuda.synchronize()
+            ok = bool(torch.equal(res2, resd) and torch.equal(qa2.s, sd)
+                      and torch.equal(qa2.q.view(torch.uint8), qd.view(torch.uint8)))
+            info["checked"].append({"tokens": M, "hidden": N, "bit_identical": ok,
+                                    "collective": "all-reduce + add + RMSNorm + quant in one kernel (ar_rmsnorm_quant_kernel)"})
         flag = torch.tensor([1 if ok else 0], device="cuda")
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         if not bool(flag.item()):
