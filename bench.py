@@ -373,6 +373,76 @@ def tp_check(stack, T, dtype, rank, world):
     return info
 
 
+def tp_8b_leg(dtype, quant, T_rank, rank, world, peaks, args):
+    """BASELINE.json configs[3]: the Qwen3-8B linear stack, INT8 per-row, tensor
+    parallel over all `world` ranks -- per-rank shards qkv [6144/tp, 4096], o [4096, 4096/tp], gate_up
+    [24576/tp, 4096], down [4096, 12288/tp]; 72 row-parallel exchanges per pass.  Prefill at T_rank x
+    world tokens and decode at 16 x world tokens, CUDA-graph replay, device-timed, max over ranks;
+    beside the step time the local GEMMs alone (no quantiser, no collective), so the part of the step
+    that is NOT tensor-core work is visible.  Random-init weights, synthetic activations."""
+    from nanovllm import _ext
+    m = MODELS["8b"]
+    stack = LinearStack(m, dtype, quant, 0, "cuda", seed=3)
+    shapes = layer_shapes(m, world)
+    out = {"model": "qwen3-8b (36 layers, hidden 4096, intermediate 12288), INT8 per-row, random-init",
+           "tp": world, "shards_per_rank": {n: [N, K] for n, N, K in shapes}}
+    steps, warm = max(args.steps // 4, 3), 3
+
+    def graph_of(fn):
+        st = torch.cuda.Stream()
+        st.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(st):
+            fn()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=st):
+                fn()
+        torch.cuda.current_stream().wait_stream(st)
+        return gr
+
+    for name, T in (("prefill", T_rank * world), ("decode", 16 * world)):
+        g = torch.Generator(device="cuda").manual_seed(5)
+        x = torch.randn(T, m["hidden"], generator=g, device="cuda", dtype=torch.float32).to(torch.bfloat16)
+        n0 = _ext.launch_count()
+        stack.forward(x)
+        launches = _ext.launch_count() - n0
+        fn = (lambda: stack.forward(x)) if args.no_graph else graph_of(lambda: stack.forward(x)).replay
+        ms = time_steps(fn, steps, warm, True)
+        acts = {}
+        for (_, N, K) in shapes:
+            if K not in acts:
+                xa = torch.randn(T, K, device="cuda", dtype=torch.float32, generator=g).to(torch.bfloat16)
+                acts[K] = _ext.quant_rows(xa, dtype)
+
+        def gemms():
+            for mods in stack.layers:
+                for mod in mods:
+                    q, sc = acts[mod.qw.shape[1]]
+                    _ext.gemm_w8a8(q, sc, mod.qw, mod._sw_kernel, None, dtype, 0)
+
+        ms_g = time_steps(gemms if args.no_graph else graph_of(gemms).replay, steps, warm, True)
+        fl = sum(2 * T * N * K for _, N, K in shapes) * m["layers"]                 # per rank
+        by = sum(N * K for _, N, K in shapes) * m["layers"]                         # weight bytes per rank
+        leg = {"tokens_per_step": T, "ms_per_step": ms, "value": T / (ms * 1e-3), "unit": "tokens/s",
+               "gpu_launches_per_step": int(launches), "local_gemms_ms": ms_g,
+               "gemm_share_of_step": ms_g / ms, "not_gemm_ms": ms - ms_g,
+               "exchanges_per_step": 2 * m["layers"],
+               "bytes_per_exchange": T * m["hidden"] * 2}
+        if name == "prefill":
+            leg.update(tflops_per_rank=fl / (ms * 1e-3) / 1e12,
+                       frac_of_tensor_peak=fl / (ms * 1e-3) / 1e12 / (2.0 * peaks["bf16"]),
+                       frac_of_nominal_4500=fl / (ms * 1e-3) / 1e12 / 4500.0)
+        else:
+            leg.update(weight_gbs_per_rank=by / (ms * 1e-3) / 1e9,
+                       frac_of_hbm_peak=by / (ms * 1e-3) / 1e9 / peaks["hbm"])
+        out[name] = leg
+    info = tp_check(stack, T_rank * world, dtype, rank, world)
+    out["tp_check"] = info["status"]
+    out["tp_collective"] = info["checked"]
+    del stack
+    torch.cuda.empty_cache()
+    return out
+
+
 def decode_leg(stack, m, T, dtype, group, world, peaks, args, dist_on):
     """The same stack at a decode-sized batch: HBM-bound (every weight byte is streamed once per
     step), reported against the measured HBM peak.  Single GPU, per-row scales: the whole stack is
@@ -827,6 +897,12 @@ def main():
     if T_rank > 16:
         decode = decode_leg(stack, m, 16 * world, dtype, group, world, peaks, args, dist_on)
 
+    # ---- BASELINE configs[3]: Qwen3-8B under tensor parallelism, in every N > 1 line of the default workload
+    tp_8b = None
+    if dist_on and group == 0 and dtype == torch.int8 and T_rank > 16 and args.model == "0.6b" \
+            and not args.no_extra_legs:
+        tp_8b = tp_8b_leg(dtype, args.quant, T_rank, rank, world, peaks, args)
+
     # ---- FP8 g=128 leg (the reference's per-group configuration), default workload only
     fp8_g128 = model_shaped = None
     if world == 1 and group == 0 and T_rank > 16 and args.model == "0.6b" and not args.no_extra_legs:
@@ -911,6 +987,8 @@ def main():
         line["fp8_g128"] = fp8_g128
     if model_shaped is not None:
         line["model_shaped"] = model_shaped
+    if tp_8b is not None:
+        line["tp_8b"] = tp_8b
     if tp_info is not None:
         line["tp_check"] = tp_info["status"]
         line["tp_collective"] = tp_info
